@@ -1,0 +1,235 @@
+"""py_twin.py -- line-by-line Python-3 twin of the reference's three Python-2 scripts.
+
+TEST INFRASTRUCTURE ONLY (see oracle/salsa_oracle.c header): an independent
+second restatement used to cross-check the C oracle on small inputs.  Pure
+Python loops, so only for small cases.
+
+PARITY UNPINNED by the reference's own tests (it has none); the reference
+scripts are Python-2 only and cannot be imported here.  Deviations from a
+literal transliteration are exactly the Python-2 semantics that Python 3
+changed, each emulated explicitly:
+  * ``str(float)``  -> ``py2_str`` ('%.12g' + '.0'),  evidence
+    fast_scaled_scores.py:39-40
+  * ``int / int``   -> ``//``                          RE_sites.py:42,71
+  * ``long(text)``  -> ``int(text)``                   make_links.py:81-82
+  * dict iteration order: Python-2 hash order is not reproducible; callers
+    compare outputs as sorted line lists.
+Files are read as latin-1 so ``str`` comparison equals byte comparison
+(make_links.py:90).
+"""
+import re
+
+
+def py2_str(x):
+    """Python-2 ``str()`` of an int or float."""
+    if isinstance(x, float):
+        if x != x:
+            return 'nan'
+        if x in (float('inf'), float('-inf')):
+            return 'inf' if x > 0 else '-inf'
+        s = '%.12g' % x
+        if '.' not in s and 'e' not in s:
+            s += '.0'
+        return s
+    return str(x)
+
+
+def make_links(mapping, directory, iteration):
+    """make_links.py:11-172.  Returns the lines written to contig_links_iteration_N
+    (in insertion order) and also writes the file."""
+    contig_lengths = {}
+    RF_counts_left = {}
+    RF_counts_right = {}
+    iteration = str(iteration)
+    # dup_links: dead code in the reference (str == int), make_links.py:20-27
+    avoid_links = {}
+    if int(iteration) > 1:
+        with open(directory + '/links_avoid_iteration_' + iteration, 'r', encoding='latin-1') as f:
+            for line in f:
+                attrs = line.split()
+                avoid_links[attrs[0] + '$' + attrs[1]] = 1
+                avoid_links[attrs[1] + '$' + attrs[0]] = 1
+    with open(directory + '/scaffold_length_iteration_' + iteration, 'r', encoding='latin-1') as cfile:
+        for line in cfile.readlines():
+            attrs = line.split()
+            contig_lengths[attrs[0]] = float(attrs[1])
+    with open(directory + '/re_counts_iteration_' + iteration, 'r', encoding='latin-1') as f:
+        for line in f:
+            attrs = line.split()
+            RF_counts_left[attrs[0]] = int(attrs[1])
+            RF_counts_right[attrs[0]] = int(attrs[2])
+
+    contig_links = {}
+    norm_score = {}
+    prev_line = ''
+    with open(mapping, 'r', encoding='latin-1', newline='\n') as f:
+        for line in f:
+            attrs = line.split()
+            if prev_line == '':
+                prev_line = line
+                continue
+            prev_attrs = prev_line.split()
+            if prev_attrs[0] != attrs[0]:
+                ks = prev_attrs[0] + '$' + attrs[0]
+                if ks in avoid_links:
+                    continue
+                prev_read = prev_attrs[3]
+                curr_read = attrs[3]
+                if prev_read.split('/')[0] == curr_read.split('/')[0]:
+                    pos1 = (int(prev_attrs[1]) + int(prev_attrs[2])) / 2.0
+                    pos2 = (int(attrs[1]) + int(attrs[2])) / 2.0
+                    key = ''
+                    if prev_attrs[0] < attrs[0]:
+                        first = prev_attrs[0]
+                        second = attrs[0]
+                    else:
+                        first = attrs[0]
+                        second = prev_attrs[0]
+                        pos1, pos2 = pos2, pos1
+                    len1 = contig_lengths[first]
+                    len2 = contig_lengths[second]
+                    l1 = len1 / 2
+                    l2 = len2 / 2
+                    r1 = l1 / len1
+                    r2 = l2 / len2
+                    if pos1 <= l1 and pos2 <= l2:
+                        key = first + ":B$" + second + ':B'
+                        norm_score[key] = RF_counts_left[first] * r1 + RF_counts_left[second] * r2
+                    if pos1 <= l1 and pos2 > len2 - l2:
+                        key = first + ":B$" + second + ':E'
+                        norm_score[key] = RF_counts_left[first] * r1 + RF_counts_right[second] * r2
+                    if pos1 > len1 - l1 and pos2 <= l2:
+                        key = first + ":E$" + second + ':B'
+                        norm_score[key] = RF_counts_right[first] * r1 + RF_counts_left[second] * r2
+                    if pos1 > len1 - l1 and pos2 > len2 - l2:
+                        key = first + ":E$" + second + ':E'
+                        norm_score[key] = RF_counts_right[first] * r1 + RF_counts_right[second] * r2
+                    if key not in contig_links and key != '':
+                        contig_links[key] = 0
+                    if key != '':
+                        contig_links[key] += 1
+            prev_line = line
+
+    out = []
+    for key in contig_links:
+        if key != '':
+            edge = key.split('$')
+            if norm_score[key] == 0:
+                score = 0
+            else:
+                score = contig_links[key] * 1.0 / norm_score[key]
+            out.append(edge[0] + '\t' + edge[1] + '\t' + py2_str(score) + '\t' + py2_str(contig_links[key]) + '\n')
+    with open(directory + '/contig_links_iteration_' + iteration, 'w', encoding='latin-1') as ofile:
+        ofile.writelines(out)
+    return out
+
+
+def fast_scaled_scores(directory, iteration):
+    """fast_scaled_scores.py:1-90, with the nx.Graph replaced by the adjacency
+    dict it is used as (G.successors raises AttributeError on an undirected
+    graph, so the ``except`` branch with G.neighbors is the live one, :22-25)."""
+    G = {}        # node -> {nbr: attrs}
+
+    def get_max_incident(start, end):
+        mx = 0
+        for e in G[start]:
+            if e != end and G[start][e]['weight'] > mx:
+                mx = G[start][e]['weight']
+        return mx
+
+    def get_max_weight(start, end):
+        return max(get_max_incident(start, end), get_max_incident(end, start))
+
+    node2weight = {}
+    path = directory + '/contig_links_iteration_' + str(iteration)
+    with open(path, 'r', encoding='latin-1') as f:
+        for line in f:
+            line = line.strip().split()
+            G.setdefault(line[0], {})
+            G.setdefault(line[1], {})
+            for k in (0, 1):
+                if line[k] not in node2weight:
+                    node2weight[line[k]] = float(line[2])
+                elif float(line[2]) >= node2weight[line[k]]:
+                    node2weight[line[k]] = float(line[2])
+            attrs = dict(weight=float(line[2]), isNeighbor="False", isGood="False", links=int(line[3]))
+            G[line[0]][line[1]] = attrs
+            G[line[1]][line[0]] = attrs
+    out = []
+    with open(path, 'r', encoding='latin-1') as f1:
+        for line in f1:
+            attrs = line.strip().split()
+            u = attrs[0]
+            v = attrs[1]
+            w = float(attrs[2])
+            max_u = node2weight.get(u, 0)
+            max_v = node2weight.get(v, 0)
+            bestAlt = max(max_u, max_v)
+            if bestAlt == w:
+                bestAlt = get_max_weight(u, v)
+            if bestAlt == 0:
+                bestAlt = 1
+            out.append(u + '\t' + v + '\t' + py2_str(w) + '\t' + py2_str(bestAlt) + '\t' + py2_str(w / bestAlt)
+                       + '\t' + str(G[u][v]['links']) + '\t' + G[u][v]['isNeighbor'] + '\t' + G[u][v]['isGood'] + '\n')
+    with open(directory + '/contig_links_scaled_iteration_' + str(iteration), 'w', encoding='latin-1') as ofile:
+        ofile.writelines(out)
+    return out
+
+
+class Exit1(Exception):
+    """stands for sys.exit(1) in RE_sites.py:13-15,48-50"""
+
+
+def parse_fasta(fh):
+    """RE_sites.py:6-28"""
+    fa = {}
+    current_short_name = None
+    for ln in fh:
+        if ln[0] == '>':
+            if ":" in ln:
+                raise Exit1("fasta records contain ':'")
+            long_name = ln[1:].rstrip()
+            current_short_name = long_name.split()[0]
+            fa[current_short_name] = []
+        else:
+            fa[current_short_name].append(ln.rstrip())
+    for short_name, nuc_list in fa.items():
+        fa[short_name] = ''.join(nuc_list)
+    return fa
+
+
+def re_sites(assembly, enzyme):
+    """RE_sites.py:30-88.  Returns the stdout lines ('id left right')."""
+    with open(assembly, 'r', encoding='latin-1', newline='\n') as fh:
+        f = parse_fasta(fh)
+    out = []
+    if enzyme == "DNASE":
+        for key in f:
+            out.append('%s %d %d' % (key, len(f[key]) // 2, len(f[key]) // 2))
+        return out
+    enzymes_input = enzyme.replace(' ', '').split(',')
+    final_enzymes = []
+    for each in enzymes_input:
+        if not re.match("^[ACGTN]+$", each):
+            raise Exit1("bad enzyme %s" % each)
+        if 'N' in each:
+            final_enzymes.append(each.replace('N', 'G'))
+            final_enzymes.append(each.replace('N', 'A'))
+            final_enzymes.append(each.replace('N', 'T'))
+            final_enzymes.append(each.replace('N', 'C'))
+        else:
+            final_enzymes.append(each)
+    for key in f:
+        seq = f[key]
+        left_count = 0
+        rigt_count = 0
+        for enzyme_ in final_enzymes:
+            pos = [m.start(0) for m in re.finditer(enzyme_, seq)]
+            length = len(seq)
+            for each in pos:
+                if each < length // 2:
+                    left_count += 1
+                else:
+                    rigt_count += 1
+        out.append('%s %d %d' % (key, left_count, rigt_count))
+    return out
