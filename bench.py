@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py -- Hi-C pairs/s into the contig-end link table (BASELINE.json's metric).
+
+    python bench.py --gpus N --steps K --warmup W           # this repo's CUDA path
+    python bench.py --impl reference ...                     # the reference's CPU path
+
+A step = one pass of the hot path (BED text -> link table) over one synthetic
+BED of the named shape, already resident in HBM when the timed region starts.
+Workload at N=1: BASELINE.json configs[1] (3.1 Gb assembly, 3,000 contigs,
+500 M pairs).  For N>1 every rank holds its own 500 M-pair shard of read pairs
+(weak scaling) and the per-GPU tables are merged by an NCCL all-reduce inside
+the step.  One JSON line is printed by rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = 'hic_pairs_per_sec_into_link_table'
+UNIT = 'pairs/s'
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        return json.load(open(p))['hbm_gbs'], 'measured'
+    return 6650.0, 'fallback'
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            a = [x.strip() for x in r.split(',')]
+            if len(a) < 7:
+                continue
+            try:
+                sm.append(float(a[0])); mx.append(float(a[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), a[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(nm)
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def build_workload(cfg_name, pairs, device, seed):
+    """Synthetic assembly + BED text generated straight into HBM, plus the
+    generator's own statement of the expected link table."""
+    from salsa_b200 import synth
+    cfg = dict(synth.CONFIGS[cfg_name])
+    asm = synth.make_assembly(seed=20261106 + int(cfg_name[-1]), **cfg)
+    n = asm.ncontig
+    chunk = 20_000_000
+    est = int(pairs * 2.02 * 47) + (1 << 20)
+    buf = torch.empty(est, dtype=torch.uint8, device=device)
+    expected = torch.zeros(n * n * 4, dtype=torch.int64, device=device)
+    pos, done, nlines = 0, 0, 0
+    while done < pairs:
+        m = min(chunk, pairs - done)
+        rec = synth.gen_records(asm, m, seed=seed * 1000 + done // chunk, device=device, read_id_base=done)
+        out = synth.format_bed(rec, out=buf[pos:])
+        keys, counts = synth.expected_links(rec, asm.lengths, n)
+        expected.index_add_(0, keys, counts)
+        pos += out.numel()
+        nlines += rec['ctg'].numel()
+        done += m
+        del rec, out, keys, counts
+    torch.cuda.synchronize()
+    return asm, buf[:pos], expected, nlines
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from salsa_b200.engine import Engine
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    pairs = args.pairs
+    asm, bed, expected, nlines = build_workload(args.config, pairs, dev, seed=rank + 1)
+    n = asm.ncontig
+    eng = Engine(local)
+    one = np.ones(n, np.int64)
+    eng.set_contigs(asm.names, asm.lengths, one, one)
+    eng.begin_links('dense')
+    st = torch.cuda.current_stream()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+
+    def step(i=None):
+        eng.table.zero_()
+        if i is not None:
+            ev[i][0].record(st)
+        eng.ingest_device(bed)
+        if i is not None:
+            ev[i][1].record(st)
+        if world > 1:
+            dist.all_reduce(eng.table)      # merge per-GPU link tables over NVLink
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record(st)
+    for i in range(args.steps):
+        step(i)
+    t1.record(st)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    total_ms = t0.elapsed_time(t1)
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([total_ms, kern_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, kern_ms = float(t[0]), float(t[1])
+    # parity at full size: the table must equal the generator's statement of the links
+    stt = eng.stats_read()
+    if world > 1:
+        dist.all_reduce(expected)
+    parity = bool(torch.equal(eng.table, expected))
+    if not parity:
+        raise SystemExit('PARITY FAILURE: link table differs from the generator\'s expected table')
+
+    # end to end through the C ABI with HOST buffers (pinned), bounded sample of the same BED
+    e2e = None
+    sample = min(bed.numel(), args.e2e_bytes)
+    cut = int((bed[:sample] == 10).nonzero()[-1].item()) + 1
+    hbuf = torch.empty(cut, dtype=torch.uint8).pin_memory()
+    hbuf.copy_(bed[:cut])
+    sample_lines = int((bed[:cut] == 10).sum().item())
+    stage = torch.empty(2 * (64 << 20), dtype=torch.uint8, device=dev)
+    hres = torch.empty(4, dtype=torch.int64).pin_memory()
+
+    def e2e_step():
+        eng.table.zero_()
+        eng.ingest_host(hbuf, stage=stage)
+        f, s, e, c = eng.links()              # D2H of the compacted link list
+        return len(c) * 16 + 32
+
+    for _ in range(2):
+        d2h = e2e_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    w0 = time.perf_counter()
+    reps = max(2, min(args.steps, 5))
+    for _ in range(reps):
+        d2h = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - w0) / reps
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t[0])
+    del hres
+    e2e_pairs = sample_lines / (nlines / pairs)
+    e2e = {'value': e2e_pairs * world / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': int(cut), 'd2h_bytes_per_step': int(d2h),
+           'sample': 'first %d bytes of the same BED from pinned host memory via salsa_bed_ingest_dense_host '
+                     '(64 MiB double-buffered chunks) + D2H of the compacted link list' % cut}
+
+    if rank != 0:
+        return
+    peak, which = peaks()
+    bed_bytes = bed.numel()
+    achieved = bed_bytes / (kern_ms * 1e-3) / 1e9
+    out = {
+        'metric': METRIC, 'value': pairs * world / (total_ms / args.steps * 1e-3), 'unit': UNIT, 'n_gpus': world,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
+        'config': {'workload': 'BASELINE configs[1]: 3.1 Gb assembly, 3,000 contigs, %d Hi-C pairs per GPU (%d BED lines, %d bytes of '
+                               '6-column BED text resident in HBM); dense link table %d cells; -e GATC,GANTC only affects scoring'
+                               % (pairs, nlines, bed_bytes, n * n * 4),
+                   'l2_policy': 'input (%.1f GB) larger than L2' % (bed_bytes / 1e9),
+                   'parallelism': 'read pairs sharded over %d GPU(s); NCCL all-reduce of the dense table' % world,
+                   'parity_full_size': 'table == generator expected table: %s; counted pairs %d' % (parity, stt.pairs)},
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                     'traffic': None, 'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
+                     'kernel': 'bed_ingest_kernel<dense>', 'algorithmic_bytes_per_launch': bed_bytes,
+                     'kernel_ms': kern_ms},
+        'e2e': e2e,
+        'gpu_launches': args.steps * 1,
+        'clocks': clocks,
+    }
+    if world == 1:
+        out['cpu_baseline'] = cpu_baseline(bed, asm, nlines / pairs, args.cpu_sample_bytes, threads=1)
+    print(json.dumps(out))
+
+
+def cpu_baseline(bed, asm, lines_per_pair, sample_bytes, threads):
+    """oracle/ C restatement of make_links.py's loop, timed on this box's host cores
+    on a bounded prefix of the same BED (the one place bench.py executes oracle/)."""
+    import oracle
+    oracle.build()
+    sample = min(bed.numel(), sample_bytes)
+    cut = int((bed[:sample] == 10).nonzero()[-1].item()) + 1
+    hb = bytes(bed[:cut].cpu().numpy())
+    n = asm.ncontig
+    one = np.ones(n, np.int64)
+    t0 = time.perf_counter()
+    res = oracle.make_links(hb, asm.names, asm.lengths.astype(float), np.ones(n, np.uint8), one, one, nthreads=threads)
+    dt = time.perf_counter() - t0
+    lines = hb.count(b'\n')
+    return {'value': lines / lines_per_pair / dt, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+            'sample': 'first %d bytes (%d lines) of the same BED, oracle/salsa_oracle.c oracle_make_links, %d thread(s), %.2f s'
+                      % (cut, lines, threads, dt), 'links': int(res['count'].sum())}
+
+
+def run_reference(args):
+    """The reference's own CPU implementation of the path.  make_links.py is
+    Python-2 only and cannot run in this image, so this arm times the oracle's C
+    restatement of its loop on all host threads (kind 'port')."""
+    rank = int(os.environ.get('RANK', 0))
+    if rank != 0:
+        return
+    import oracle
+    from salsa_b200 import synth
+    oracle.build()
+    cfg = dict(synth.CONFIGS[args.config])
+    asm = synth.make_assembly(seed=20261106 + int(args.config[-1]), **cfg)
+    n = asm.ncontig
+    sample_pairs = args.ref_pairs
+    rec = synth.gen_records(asm, sample_pairs, seed=1000, device='cpu')
+    bed = bytes(synth.format_bed(rec).numpy())
+    nlines = rec['ctg'].numel()
+    threads = os.cpu_count() or 1
+    one = np.ones(n, np.int64)
+
+    def step():
+        return oracle.make_links(bed, asm.names, asm.lengths.astype(float), np.ones(n, np.uint8), one, one, nthreads=threads)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = step()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = sample_pairs / dt
+    out = {'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': UNIT, 'n_gpus': int(os.environ.get('WORLD_SIZE', 1)),
+           'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+           'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
+           'config': {'workload': 'BASELINE configs[1] shape (3.1 Gb assembly, 3,000 contigs); each step = a bounded sample of '
+                                  '%d pairs (%d BED lines, %d bytes) of that workload' % (sample_pairs, nlines, len(bed))},
+           'cpu_baseline': {'value': val, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                            'sample': '%d pairs per step; oracle/salsa_oracle.c (C restatement of make_links.py:60-146), '
+                                      'byte-range sharded over %d threads' % (sample_pairs, threads)},
+           'e2e': {'value': val, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+           'gpu_launches': 0, 'links': int(res['count'].sum())}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--config', default='cfg2')
+    ap.add_argument('--pairs', type=int, default=None, help='pairs per GPU (default: the config\'s)')
+    ap.add_argument('--e2e-bytes', type=int, default=4 << 30)
+    ap.add_argument('--cpu-sample-bytes', type=int, default=1 << 30)
+    ap.add_argument('--ref-pairs', type=int, default=10_000_000)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
+    if args.pairs is None:
+        from salsa_b200 import synth
+        args.pairs = synth.CONFIGS[args.config]['pairs']
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

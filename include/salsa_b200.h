@@ -1,0 +1,178 @@
+/*
+ * salsa_b200.h -- C ABI of libsalsa_b200.so: SALSA's Hi-C link-scoring hot
+ * path as hand-written CUDA for B200 (sm_100a).
+ *
+ * The reference (marbl/SALSA) has NO in-process plugin / FFI interface: its
+ * hot path sits behind process + file boundaries driven by run_pipeline.py
+ * (SURVEY.md section 8(b)).  Each entry point below therefore cites the
+ * reference PROGRAM (file:line of the loop) whose work it replaces; the
+ * drop-in step scripts in salsa_b200/ (make_links.py, RE_sites.py,
+ * fast_scaled_scores.py, break_contigs*.py) keep the reference's argv and
+ * file formats and call these functions through ctypes.  INTEGRATION.md shows
+ * the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types.
+ *   - "d_" arguments are DEVICE pointers owned by the caller (e.g.
+ *     torch.Tensor.data_ptr()); "h_" arguments are HOST pointers.  The
+ *     library never frees caller memory.
+ *   - every function returns 0 on success, < 0 on error; the message is in
+ *     salsa_last_error() (thread local).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *     Work is enqueued asynchronously unless the function is documented to
+ *     synchronise.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry
+ *     point fails with SALSA_ERR_CUDA.
+ */
+#ifndef SALSA_B200_H
+#define SALSA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SALSA_OK 0
+#define SALSA_ERR_CUDA (-1)
+#define SALSA_ERR_ARG (-2)
+#define SALSA_ERR_NOMEM (-3)
+#define SALSA_ERR_UNSUPPORTED (-4)
+
+/* Data errors found by the BED kernels, mirroring the Python exception the
+ * reference would die with (run_pipeline.py:166-170 turns any of them into
+ * "step failed"). Reported in salsa_ingest_stats.err_code. */
+#define SALSA_DATA_OK 0
+#define SALSA_DATA_INDEX_ERROR 1   /* < 1 or < 4 fields   make_links.py:71,76-77  */
+#define SALSA_DATA_VALUE_ERROR 2   /* bad start/end text  make_links.py:81-82     */
+#define SALSA_DATA_KEY_ERROR 3     /* unknown contig / no RE counts  make_links.py:101-113 */
+#define SALSA_DATA_ZERO_DIV 4      /* zero-length contig  make_links.py:106-107   */
+#define SALSA_DATA_LINE_TOO_LONG 5 /* a line's first four fields, or a whole line
+                                      that precedes a tile boundary, exceed
+                                      SALSA_MAX_LINE bytes (library limit)       */
+
+#define SALSA_MAX_LINE 1024        /* bytes; see SALSA_DATA_LINE_TOO_LONG */
+
+typedef struct salsa_ctx salsa_ctx;
+
+const char *salsa_last_error(void);
+int salsa_version(void);
+
+/* One context per (process, device).  Holds the device-side contig table. */
+int salsa_ctx_create(int device, salsa_ctx **out);
+void salsa_ctx_destroy(salsa_ctx *ctx);
+
+/*
+ * Contig table: replaces the three host dicts of make_links.py:37-48
+ * (contig_lengths, RF_counts_left, RF_counts_right) and the string compare of
+ * make_links.py:90.
+ *   h_names_blob / h_name_off[n+1] : contig names, STRICTLY INCREASING in byte
+ *       order (memcmp, shorter prefix first) so that id order == Python-2
+ *       string order; the id of a contig is its index.
+ *   h_len_floor[i] : floor(float(length)); the B/E rule of make_links.py:108-139
+ *       is exactly  B <=> start+end <= floor(len)  (DESIGN.md).
+ *   h_flags[i]     : SALSA_CTG_* bits.
+ * Names that appear only in links_avoid_iteration_N are listed too, without
+ * SALSA_CTG_HAS_LEN.  Synchronises.
+ */
+#define SALSA_CTG_HAS_LEN 1u
+#define SALSA_CTG_HAS_RE 2u
+int salsa_names_build(salsa_ctx *ctx, const char *h_names_blob, const int64_t *h_name_off, int32_t n,
+                      const int64_t *h_len_floor, const uint32_t *h_flags);
+int32_t salsa_names_count(const salsa_ctx *ctx);
+
+/* links_avoid_iteration_N (make_links.py:29-35): id pairs, both orders implied.
+ * n == 0 clears the set.  Synchronises. */
+int salsa_avoid_set(salsa_ctx *ctx, const int32_t *h_id_pairs, int32_t npairs);
+
+/*
+ * Ingest statistics, 4 x uint64 in DEVICE memory, accumulated across calls.
+ * Reset with salsa_ingest_stats_reset before the first chunk.
+ *   [0] err   : min over errors of (byte offset of the offending line << 8 | code);
+ *               UINT64_MAX when clean
+ *   [1] lines : lines seen as "current" (make_links.py:60 minus the first line)
+ *   [2] pairs : adjacent-line pairs counted into the table
+ *   [3] reserved
+ */
+typedef struct {
+    uint64_t err_offset;
+    int32_t err_code;
+    uint64_t lines;
+    uint64_t pairs;
+} salsa_ingest_stats;
+int salsa_ingest_stats_reset(uint64_t *d_stats, void *stream);
+/* copies to the host and decodes; synchronises the stream */
+int salsa_ingest_stats_read(const uint64_t *d_stats, salsa_ingest_stats *h_out, void *stream);
+
+/*
+ * BED ingest -> dense contig-end link histogram.
+ * Replaces make_links.py:60-146 (the per-line loop: split, adjacent-line
+ * pairing, read-name test, end classification, contig_links[key] += 1).
+ *
+ *   d_bed[0..nbytes) : raw BED text whose FIRST byte starts a line.  Every
+ *       adjacent-line pair inside the buffer is evaluated exactly as the
+ *       reference evaluates it; the first line only ever plays "previous"
+ *       (make_links.py:66-68).  To ingest a file in chunks (or shards on
+ *       several GPUs) start each chunk at the first byte of the previous
+ *       chunk's LAST line: chunks overlap by exactly one line.  With a
+ *       non-empty avoid set a chunk must additionally start on a line whose
+ *       contig is in no avoid pair (salsa_bed_split finds such boundaries).
+ *   d_table : uint64 [n*n*4], n = salsa_names_count(); cell
+ *       ((first*n + second)*4 + ends) with first < second, ends bit1 = first
+ *       is 'E', bit0 = second is 'E'.  Counts are ADDED (zero it first).
+ *   base_offset : byte offset of d_bed[0] in the whole file (only used to
+ *       report error positions).
+ * Asynchronous on `stream`.  No scratch memory, no allocation.
+ */
+int salsa_bed_ingest_dense(salsa_ctx *ctx, const void *d_bed, size_t nbytes, uint64_t base_offset,
+                           uint64_t *d_table, uint64_t *d_stats, void *stream);
+
+/*
+ * Same scan, sparse link table for high-cardinality assemblies (dense table
+ * would not fit): open-addressing hash table in caller memory.
+ *   d_keys   : uint64 [capacity] (capacity a power of two), initialised to
+ *              UINT64_MAX by salsa_sparse_reset; key = (first*n + second)*4 + ends
+ *   d_counts : uint64 [capacity], zeroed by salsa_sparse_reset
+ * If the table fills up the err code is SALSA_DATA_TABLE_FULL.
+ */
+#define SALSA_DATA_TABLE_FULL 6
+int salsa_sparse_reset(uint64_t *d_keys, uint64_t *d_counts, size_t capacity, void *stream);
+int salsa_bed_ingest_sparse(salsa_ctx *ctx, const void *d_bed, size_t nbytes, uint64_t base_offset,
+                            uint64_t *d_keys, uint64_t *d_counts, size_t capacity,
+                            uint64_t *d_stats, void *stream);
+
+/*
+ * Convenience for host-resident BEDs (what make_links.py does with a file):
+ * streams h_bed through two device staging buffers of `chunk_bytes` each
+ * (caller-owned, d_stage[2*chunk_bytes]) with copies overlapped with the
+ * kernel, splitting at line starts.  h_bed should be pinned for full PCIe
+ * speed.  Synchronises before returning.
+ */
+int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, size_t nbytes, void *d_stage,
+                                size_t chunk_bytes, uint64_t *d_table, uint64_t *d_stats);
+
+/*
+ * Table -> ordered edge list (replaces the dict walk of make_links.py:161-169;
+ * the reference's own order is Python-2 dict order, which no consumer uses).
+ * Writes the (key, count) of every non-empty cell in ascending cell order.
+ *   dense table : d_keys == NULL, the cell index is the key -> output sorted
+ *   sparse table: d_keys = the hash table's keys -> output in slot order; sort
+ *                 it with salsa_sort_pairs_u64
+ * d_scratch: salsa_links_compact_scratch_bytes(ncells) bytes.  With
+ * d_out_keys == NULL only counts.  *h_n receives the number of links.
+ * Synchronises the stream.
+ */
+size_t salsa_links_compact_scratch_bytes(size_t ncells);
+int salsa_links_compact(const uint64_t *d_keys, const uint64_t *d_counts, size_t ncells,
+                        uint64_t *d_out_keys, uint64_t *d_out_counts, size_t out_capacity,
+                        void *d_scratch, uint64_t *h_n, void *stream);
+/* Radix sort of (key, value) pairs by key (CUB; off the hot path).  Call with
+ * d_tmp == NULL to get the scratch size in *tmp_bytes. */
+int salsa_sort_pairs_u64(uint64_t *d_keys_in, uint64_t *d_vals_in, uint64_t *d_keys_out,
+                         uint64_t *d_vals_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SALSA_B200_H */

@@ -1,0 +1,259 @@
+"""GPU parity tests of the BED ingest path (through the C ABI) against the oracle."""
+import gzip
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+
+
+@pytest.fixture(scope='module')
+def eng():
+    from salsa_b200.engine import Engine
+    e = Engine(0)
+    yield e
+    e.close()
+
+
+def oracle_dict(o, bed, names, lengths, has_re=None, avoid=()):
+    n = len(names)
+    hr = np.ones(n, np.uint8) if has_re is None else has_re
+    res = o.make_links(bed, names, np.asarray(lengths, float), hr, np.ones(n, np.int64), np.ones(n, np.int64), avoid)
+    return {(names[a], names[b], int(e)): int(c) for a, b, e, c in zip(res['first'], res['second'], res['ends'], res['count'])}, res
+
+
+def gpu_dict(eng, bed, names, lengths, mode='dense', offset=0, has_re=None, via='device', chunks=None):
+    n = len(names)
+    eng.set_contigs(names, np.asarray(lengths, np.int64), np.ones(n, np.int64), np.ones(n, np.int64), has_re)
+    eng.begin_links(mode, sparse_capacity=1 << 16)
+    if via == 'device':
+        raw = torch.zeros(offset + len(bed) + 64, dtype=torch.uint8, device=eng.device)
+        raw[:offset] = 65      # junk before the caller's pointer: must never be read as data
+        raw[offset + len(bed):] = 66
+        raw[offset:offset + len(bed)] = torch.frombuffer(bytearray(bed), dtype=torch.uint8).to(eng.device) if len(bed) else raw[0:0]
+        if chunks is None:
+            eng.ingest_device(raw[offset:offset + len(bed)])
+        else:
+            for lo, hi in chunks:
+                eng.ingest_device(raw[offset + lo:offset + hi], base_offset=lo)
+    else:
+        buf = np.frombuffer(bed, dtype=np.uint8)
+        eng.ingest_host(buf, chunk_bytes=via)
+    st = eng.stats_read()
+    f, s, e, c = eng.links()
+    d = {(eng.names[a], eng.names[b], int(x)): int(y) for a, b, x, y in zip(f, s, e, c)}
+    assert sum(d.values()) == st.pairs
+    return d, st
+
+
+def test_golden_case(eng, oracle_lib):
+    bed = gzip.open(os.path.join(GOLD, 'links_case.bed.gz'), 'rb').read()
+    lens = [ln.split() for ln in gzip.open(os.path.join(GOLD, 'links_case.len.gz'), 'rb').read().splitlines()]
+    names = [a[0] for a in lens]
+    L = [int(a[1]) for a in lens]
+    want, res = oracle_dict(oracle_lib, bed, names, L)
+    got, st = gpu_dict(eng, bed, names, L)
+    assert got == want
+    assert st.pairs == res['npairs_counted']
+    assert st.lines == bed.count(b'\n') - 1
+    # and the committed twin vectors (counts column)
+    import json
+    g = json.load(open(os.path.join(GOLD, 'links_twin.json')))
+    tw = {}
+    for ln in g['links']:
+        a, b, sc, cnt = ln.split()
+        tw[(a.split(':')[0].encode(), b.split(':')[0].encode(), (a[-1] == 'E') * 2 + (b[-1] == 'E'))] = int(cnt)
+    assert got == tw
+
+
+@pytest.mark.parametrize('offset', [0, 1, 7, 15, 16, 33])
+def test_misaligned_pointer(eng, oracle_lib, offset):
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=9, genome=100000, npairs=1500, seed=3)
+    want, _ = oracle_dict(oracle_lib, bed, asm.names, asm.lengths)
+    got, _ = gpu_dict(eng, bed, asm.names, asm.lengths, offset=offset)
+    assert got == want
+
+
+@pytest.mark.parametrize('mode', ['dense', 'sparse'])
+@pytest.mark.parametrize('seed', [1, 2, 3])
+def test_random_cases(eng, oracle_lib, seed, mode):
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=7 + 30 * seed, genome=400000 * seed, npairs=4000 * seed, seed=10 + seed,
+                                     triple=0.05, noise=0.2)
+    want, _ = oracle_dict(oracle_lib, bed, asm.names, asm.lengths)
+    got, _ = gpu_dict(eng, bed, asm.names, asm.lengths, mode=mode)
+    assert got == want
+    keys, counts = synth.expected_links(rec, asm.lengths, asm.ncontig)
+    assert sum(want.values()) == int(counts.sum())
+
+
+def _messy_bed(rng, names, nlines, L):
+    """whitespace variety, long/short names, \\r\\n, extra columns, missing trailing newline"""
+    out = []
+    seps = [b'\t', b' ', b'  ', b'\t ', b' \t\t']
+    r = 0
+    for i in range(nlines):
+        if rng.random() < 0.6:
+            r += 1
+        c = names[int(rng.integers(0, len(names)))]
+        s = int(rng.integers(0, 5000))
+        e = s + int(rng.integers(1, 300))
+        sep = seps[int(rng.integers(0, len(seps)))]
+        rd = b'r%d' % r
+        if rng.random() < 0.7:
+            rd += b'/%d' % int(rng.integers(1, 3))
+        if rng.random() < 0.1:
+            rd += b'/x/y'
+        lead = b' ' if rng.random() < 0.05 else b''
+        tail = [b'', b'\t60\t+', b' extra col', b'\r', b'\t' * 3][int(rng.integers(0, 5))]
+        sg = b'+' if rng.random() < 0.05 else b''
+        out.append(lead + c + sep + sg + b'%d' % s + sep + b'%d' % e + sep + rd + tail)
+    return b'\n'.join(out)
+
+
+@pytest.mark.parametrize('seed', [0, 1, 2, 3])
+def test_messy_text(eng, oracle_lib, seed):
+    rng = np.random.default_rng(seed)
+    names = [b'c', b'ctg1', b'ctg10', b'ctg2', b'a_very_long_contig_name_over_16_bytes_A', b'a_very_long_contig_name_over_16_bytes_B',
+             b'exactly16bytes__', b'exactly16bytes_', b'X' * 17, b'X' * 40, b'scaffold_12', b'Ctg1']
+    L = [int(rng.integers(2000, 6000)) for _ in names]
+    bed = _messy_bed(rng, names, 6000, L) + (b'\n' if seed % 2 else b'')
+    want, _ = oracle_dict(oracle_lib, bed, names, L)
+    assert len(want) > 50
+    got, _ = gpu_dict(eng, bed, names, L)
+    assert got == want
+
+
+def test_many_short_lines_fallback_path(eng, oracle_lib):
+    # > 256 line starts inside one warp's 4 KB region -> the 2 KB sub-range path
+    rng = np.random.default_rng(5)
+    names = [b'a', b'b', b'c']
+    L = [10, 10, 10]
+    lines = []
+    for i in range(40000):
+        lines.append(names[int(rng.integers(0, 3))] + b' %d %d r%d' % (rng.integers(0, 9), rng.integers(0, 9), i // 2))
+    bed = b'\n'.join(lines) + b'\n'
+    want, _ = oracle_dict(oracle_lib, bed, names, L)
+    got, st = gpu_dict(eng, bed, names, L)
+    assert got == want and st.lines == 39999
+    # same contig on both sides never inspects further fields: 1-field lines are fine
+    bed2 = b'a\n' * 5000 + b'a 1 2 r/1\nb 3 4 r/2\n'
+    want2, _ = oracle_dict(oracle_lib, bed2, names, L)
+    got2, _ = gpu_dict(eng, bed2, names, L)
+    assert got2 == want2 == {(b'a', b'b', 0): 1}
+
+
+def test_chunked_equals_whole(eng, oracle_lib):
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=15, genome=300000, npairs=5000, seed=21, triple=0.05)
+    want, _ = oracle_dict(oracle_lib, bed, asm.names, asm.lengths)
+    # chunk boundaries: each chunk starts at the first byte of the previous chunk's last line
+    nl = [i for i, ch in enumerate(bed) if ch == 10]
+    cuts = [nl[len(nl) // 5], nl[len(nl) // 2], nl[len(nl) // 2 + 1], nl[-3]]
+    chunks, lo = [], 0
+    for c in cuts:
+        hi = c + 1                                   # chunk ends after line ending at c
+        chunks.append((lo, hi))
+        lo = bed.rfind(b'\n', 0, c) + 1              # start of that last line
+    chunks.append((lo, len(bed)))
+    got, _ = gpu_dict(eng, bed, asm.names, asm.lengths, chunks=chunks)
+    assert got == want
+
+
+@pytest.mark.parametrize('chunk', [4096, 65536, 1 << 20])
+def test_host_streaming(eng, oracle_lib, chunk):
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=15, genome=300000, npairs=5000, seed=22)
+    want, _ = oracle_dict(oracle_lib, bed, asm.names, asm.lengths)
+    got, _ = gpu_dict(eng, bed, asm.names, asm.lengths, via=chunk)
+    assert got == want
+
+
+def test_empty_and_tiny(eng, oracle_lib):
+    names, L = [b'A', b'B'], [1000, 2000]
+    for bed in (b'', b'\n', b'A 1 2 r/1', b'A 1 2 r/1\n', b'A 100 200 r1/1\nB 1900 1990 r1/2\n', b'A 100 200 r1/1\nB 1900 1990 r1/2'):
+        got, st = gpu_dict(eng, bed, names, L)
+        if bed.count(b'B'):
+            assert got == {(b'A', b'B', 1): 1}        # KAT-links: A:B  B:E
+        else:
+            assert got == {}
+
+
+def test_midpoint_rule(eng):
+    names, L = [b'A', b'B'], [1001, 1001]
+    for se, e in ((1001, 0), (1002, 3), (1000, 0)):
+        bed = b'A 0 %d r/1\nB 0 %d r/2\n' % (se, se)
+        got, _ = gpu_dict(eng, bed, names, L)
+        assert got == {(b'A', b'B', e): 1}
+
+
+def test_data_errors(eng, oracle_lib):
+    from salsa_b200.engine import DataError
+    names, L = [b'A', b'B'], [10, 10]
+    cases = [
+        (b'A 1 2 r/1\n\nB 1 2 r/2\n', 1, -1),      # blank line: IndexError
+        (b'A 1 2 r/1\nB 1 2\n', 1, -1),            # < 4 fields, contigs differ
+        (b'A 1 x r/1\nB 1 2 r/2\n', 2, -2),        # ValueError
+        (b'A 1 2 r/1\nZ 1 2 r/2\n', 3, -3),        # KeyError (unknown contig)
+    ]
+    for bed, code, ocode in cases:
+        with pytest.raises(oracle_lib.OracleError) as oe:
+            oracle_dict(oracle_lib, bed, names, L)
+        assert oe.value.code == ocode
+        with pytest.raises(DataError) as ge:
+            gpu_dict(eng, bed, names, L)
+        assert ge.value.code == code
+    # zero-length contig, missing RE counts
+    with pytest.raises(DataError) as ge:
+        gpu_dict(eng, b'A 1 2 r/1\nB 1 2 r/2\n', names, [0, 10])
+    assert ge.value.code == 4
+    with pytest.raises(DataError) as ge:
+        gpu_dict(eng, b'A 1 2 r/1\nB 1 2 r/2\n', names, [10, 10], has_re=np.array([1, 0]))
+    assert ge.value.code == 3
+    # errors are lazy like the reference: unknown contigs / bad numbers that are never needed are fine
+    got, _ = gpu_dict(eng, b'Z x y r/1\nZ 1 2 q/2\nA 1 2 s/1\nQ 1 2 t/1\n', names, L)
+    assert got == {}
+    # error offset = byte offset of the offending (current) line
+    with pytest.raises(DataError) as ge:
+        gpu_dict(eng, b'A 1 2 r/1\nA 1 2 r/2\nA 1 x q/1\nB 1 2 q/2\n', names, L)
+    assert ge.value.code == 2 and ge.value.offset == 30
+
+
+def test_line_too_long(eng):
+    from salsa_b200.engine import DataError
+    names, L = [b'A', b'B'], [10, 10]
+    # long TAIL columns are fine as long as the line stays within the halo
+    bed = b'A 1 2 r/1 ' + b'x' * 900 + b'\nB 1 2 r/2\n'
+    got, _ = gpu_dict(eng, bed, names, L)
+    assert got == {(b'A', b'B', 0): 1}
+    # a 3 KB line straddling a tile boundary cannot be located from the next tile
+    pad = b'A 1 2 z/1\n' * 3270          # ~32.7 KB: next line straddles byte 32768
+    bed = pad + b'A 1 2 r/1 ' + b'x' * 3000 + b'\nB 1 2 r/2\n'
+    with pytest.raises(DataError) as ge:
+        gpu_dict(eng, bed, names, L)
+    assert ge.value.code == 5
+
+
+def test_device_generated_large(eng):
+    """2M pairs generated in HBM; the table must equal the generator's own
+    statement of the links (never parsed from text)."""
+    from salsa_b200 import synth
+    asm = synth.make_assembly(ncontig=300, genome=30_000_000, len_lo=20_000, len_hi=400_000, nchrom=5, seed=77)
+    rec = synth.gen_records(asm, 2_000_000, seed=78, device='cuda')
+    bed = synth.format_bed(rec)
+    keys, counts = synth.expected_links(rec, asm.lengths, asm.ncontig)
+    n = asm.ncontig
+    eng.set_contigs(asm.names, asm.lengths, np.ones(n, np.int64), np.ones(n, np.int64))
+    for mode in ('dense', 'sparse'):
+        eng.begin_links(mode, sparse_capacity=1 << 20)
+        eng.ingest_device(bed)
+        st = eng.stats_read()
+        f, s, e, c = eng.links()
+        k = ((f * n + s) << 2) | e
+        assert (k == keys.cpu().numpy()).all() and (c == counts.cpu().numpy()).all()
+        assert st.pairs == int(counts.sum()) and st.lines == rec['ctg'].numel() - 1
