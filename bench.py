@@ -38,7 +38,7 @@ def peaks():
 
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region."""
-    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+    Q = ('timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
          'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
 
     def __init__(self, index):
@@ -47,7 +47,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                          '--format=csv,noheader,nounits', '-lms', '50'],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -56,7 +56,11 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.rows.append(ln.strip())
+            self.rows.append((time.time(), ln.strip()))
+
+    def mark(self):
+        """start of the timed region (the sampler itself starts earlier: nvidia-smi needs ~0.2 s to come up)"""
+        self.t0 = time.time()
 
     def stop(self):
         if not self.proc:
@@ -67,8 +71,11 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
-            a = [x.strip() for x in r.split(',')]
+        t1 = time.time()
+        for ts, r in self.rows:
+            if ts < getattr(self, 't0', 0) or ts > t1:
+                continue
+            a = [x.strip() for x in r.split(',')][1:]
             if len(a) < 7:
                 continue
             try:
@@ -138,21 +145,24 @@ def run_ours(args):
         if world > 1:
             dist.all_reduce(eng.table)      # merge per-GPU link tables over NVLink
 
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    sampler.mark()
+    torch.cuda.profiler.start()          # lets `ncu --profile-from-start off` see only the timed region
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     t0.record(st)
     for i in range(args.steps):
         step(i)
     t1.record(st)
     torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -173,6 +183,10 @@ def run_ours(args):
 
     # end to end through the C ABI with HOST buffers (pinned), bounded sample of the same BED
     e2e = None
+    if args.no_extras:
+        if rank == 0:
+            print(json.dumps({'profile_run': True, 'kernel_ms': kern_ms, 'ms_per_step': total_ms / args.steps}))
+        return
     sample = min(bed.numel(), args.e2e_bytes)
     cut = int((bed[:sample] == 10).nonzero()[-1].item()) + 1
     hbuf = torch.empty(cut, dtype=torch.uint8).pin_memory()
@@ -301,13 +315,14 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--config', default='cfg2')
     ap.add_argument('--pairs', type=int, default=None, help='pairs per GPU (default: the config\'s)')
     ap.add_argument('--e2e-bytes', type=int, default=4 << 30)
     ap.add_argument('--cpu-sample-bytes', type=int, default=1 << 30)
+    ap.add_argument('--no-extras', action='store_true', help='timed region only (for ncu runs): no e2e / cpu legs')
     ap.add_argument('--ref-pairs', type=int, default=10_000_000)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup

@@ -231,9 +231,19 @@ def test_line_too_long(eng):
     bed = b'A 1 2 r/1 ' + b'x' * 900 + b'\nB 1 2 r/2\n'
     got, _ = gpu_dict(eng, bed, names, L)
     assert got == {(b'A', b'B', 0): 1}
-    # a 3 KB line straddling a tile boundary cannot be located from the next tile
-    pad = b'A 1 2 z/1\n' * 3270          # ~32.7 KB: next line straddles byte 32768
+    # a long line that starts less than SALSA_MAX_LINE before a tile boundary is still found
+    pad = b'A 1 2 z/1\n' * 3270          # 32.7 KB: the next line straddles byte 32768
     bed = pad + b'A 1 2 r/1 ' + b'x' * 3000 + b'\nB 1 2 r/2\n'
+    got, _ = gpu_dict(eng, bed, names, L)
+    assert got == {(b'A', b'B', 0): 1}
+    # ... but not one that starts more than SALSA_MAX_LINE before it: library limit, reported
+    pad = b'A 1 2 z/1\n' * 3070
+    bed = pad + b'A 1 2 r/1 ' + b'x' * 3000 + b'\nB 1 2 r/2\n'
+    with pytest.raises(DataError) as ge:
+        gpu_dict(eng, bed, names, L)
+    assert ge.value.code == 5
+    # the first four fields themselves running past the halo
+    bed = b'A 1 2 z/1\n' * 3276 + b'A 1 2 ' + b'r' * 1100 + b'/1\nB 1 2 ' + b'r' * 1100 + b'/2\n'
     with pytest.raises(DataError) as ge:
         gpu_dict(eng, bed, names, L)
     assert ge.value.code == 5
