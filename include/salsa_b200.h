@@ -172,6 +172,72 @@ int salsa_links_compact(const uint64_t *d_keys, const uint64_t *d_counts, size_t
 int salsa_sort_pairs_u64(uint64_t *d_keys_in, uint64_t *d_vals_in, uint64_t *d_keys_out,
                          uint64_t *d_vals_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream);
 
+/*
+ * Python-2 str(float) on the device.  The reference passes scores between
+ * programs as text written with str(float) = '%.12g' (make_links.py:169,
+ * fast_scaled_scores.py:86; 12 digits evidenced by fast_scaled_scores.py:39-40),
+ * so the next program sees float(str(x)).  For each x:
+ *   digits : the 12-digit integer D of '%.12g' (sign carried; 0 for x == 0)
+ *   exp10  : decimal exponent k of the leading digit (x ~ D * 10^(k-11))
+ *   w12    : the double nearest to that decimal, i.e. float(str(x))
+ * Exact (320-bit integer arithmetic, round-half-even on the binary value).
+ */
+int salsa_g12(const double *d_x, size_t n, int64_t *d_digits, int32_t *d_exp10, double *d_w12, void *stream);
+
+/*
+ * Link scores.  Replaces make_links.py:104-137 (norm = RE*0.5 + RE*0.5 with
+ * left counts for a 'B' end and right counts for an 'E' end) and :165-168
+ * (score = 0 if norm == 0 else count*1.0/norm), plus the decimal round trip
+ * into fast_scaled_scores.py:48,71.
+ *   d_keys/d_counts : compacted table (salsa_links_compact), key = (first*n+second)*4+ends
+ *   d_re_left/right : int64 [ncontig] by contig id
+ * Outputs per link: score (raw double), is_int0 (the reference prints the int
+ * literal 0), digits/exp10/w12 as in salsa_g12, and the two node ids
+ * u = first*2 + (first end is E), v = second*2 + (second end is E).
+ */
+int salsa_links_score(const uint64_t *d_keys, const uint64_t *d_counts, size_t n, int32_t ncontig,
+                      const int64_t *d_re_left, const int64_t *d_re_right, double *d_score,
+                      uint8_t *d_is_int0, int64_t *d_digits, int32_t *d_exp10, double *d_w12,
+                      int32_t *d_u, int32_t *d_v, void *stream);
+
+/*
+ * Best-buddy ratios.  Replaces fast_scaled_scores.py:35-89: node2weight (max
+ * weight per contig end, :47-57), bestAlt = max of the two ends' best weights,
+ * replaced -- when this edge IS the best at both ends -- by the best weight
+ * among the OTHER edges at either end (:13-33,79-82), 0 -> int 1 (:83-84),
+ * ratio = w / bestAlt (:86).  Weights must be >= 0.
+ *   d_u, d_v : node ids in [0, nnodes); the graph must be simple
+ *   d_w      : float(text of column 3)  (w12 of salsa_links_score)
+ *   d_scratch: salsa_scaled_scratch_bytes(nnodes) bytes of device memory
+ * Outputs per edge: best_alt, is_int1, ratio, and the str(float) digits of
+ * ratio and of best_alt.
+ */
+size_t salsa_scaled_scratch_bytes(int32_t nnodes);
+int salsa_scaled_scores(const int32_t *d_u, const int32_t *d_v, const double *d_w, size_t n, int32_t nnodes,
+                        void *d_scratch, double *d_best_alt, uint8_t *d_is_int1, double *d_ratio,
+                        int64_t *d_ratio_digits, int32_t *d_ratio_exp10, int64_t *d_best_digits,
+                        int32_t *d_best_exp10, void *stream);
+
+/*
+ * Host-side text assembly (no float conversion happens here: text is built
+ * from the integer digits the device produced).
+ * salsa_format_g12   : str(float) strings, concatenated; h_off[n+1] offsets
+ * salsa_format_links : contig_links_iteration_N lines (make_links.py:169);
+ *                      returns bytes written or -1
+ * salsa_format_scaled: contig_links_scaled_iteration_N lines
+ *                      (fast_scaled_scores.py:86); returns bytes written or -1
+ */
+int salsa_format_g12(const int64_t *h_digits, const int32_t *h_exp10, size_t n, char *h_out, size_t out_cap,
+                     int64_t *h_off);
+int64_t salsa_format_links(const char *names_blob, const int64_t *name_off, const int64_t *first,
+                           const int64_t *second, const uint8_t *ends, const int64_t *count,
+                           const int64_t *digits, const int32_t *exp10, const uint8_t *is_int0, size_t n,
+                           char *out, size_t out_cap);
+int64_t salsa_format_scaled(const char *node_blob, const int64_t *node_off, const int32_t *u, const int32_t *v,
+                            const int64_t *w_digits, const int32_t *w_exp10, const int64_t *b_digits,
+                            const int32_t *b_exp10, const uint8_t *b_is_int1, const int64_t *r_digits,
+                            const int32_t *r_exp10, const int64_t *links, size_t n, char *out, size_t out_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,18 @@
+"""Shared helpers of the drop-in step scripts (same argv and files as the reference's programs)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+_ENGINE = None
+
+
+def engine():
+    """One Engine per process (device from SALSA_B200_DEVICE, default 0)."""
+    global _ENGINE
+    if _ENGINE is None:
+        from salsa_b200.engine import Engine
+        _ENGINE = Engine(int(os.environ.get('SALSA_B200_DEVICE', '0')))
+    return _ENGINE

@@ -1,0 +1,450 @@
+// links_score.cu -- enzyme-normalised link scores and best-buddy ratios.
+//
+// Replaces, for every link of the table:
+//   make_links.py:104-137,165-168   norm = RE[first]*0.5 + RE[second]*0.5, score = count/norm
+//   make_links.py:169 -> fast_scaled_scores.py:48,71   the score crosses a text file as
+//        Python-2 str(float) = '%.12g', so the value the next program sees is the
+//        double nearest to the 12-significant-digit decimal of the score
+//   fast_scaled_scores.py:47-57     node2weight[end] = max weight over incident edges
+//   fast_scaled_scores.py:13-33,79-86  bestAlt / ratio (best-buddy second-best ratio)
+//
+// The decimal round trip is done exactly, with 320-bit integers on the device:
+// g12(x) yields the 12-digit integer D and decimal exponent k of '%.12g' % x
+// (round-half-even on the exact binary value, like glibc/CPython) and the
+// correctly rounded double of D*10^(k-11).  The host only assembles text from
+// (D, k); it never converts a float.
+#include "common.cuh"
+
+namespace {
+
+constexpr int NL = 10;   // 32-bit limbs: 320 bits (largest intermediate < 2^250)
+
+struct Big {
+    uint32_t w[NL];
+};
+
+__device__ __forceinline__ void big_set(Big &a, uint64_t v)
+{
+#pragma unroll
+    for (int i = 0; i < NL; i++) a.w[i] = 0;
+    a.w[0] = (uint32_t)v;
+    a.w[1] = (uint32_t)(v >> 32);
+}
+
+__device__ __forceinline__ void big_mul_small(Big &a, uint32_t m)
+{
+    uint64_t c = 0;
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        uint64_t t = (uint64_t)a.w[i] * m + c;
+        a.w[i] = (uint32_t)t;
+        c = t >> 32;
+    }
+}
+
+__device__ void big_mul_pow10(Big &a, int p)
+{
+    while (p >= 9) { big_mul_small(a, 1000000000u); p -= 9; }
+    uint32_t m = 1;
+    while (p-- > 0) m *= 10u;
+    if (m > 1) big_mul_small(a, m);
+}
+
+__device__ void big_shl(Big &a, int bits)
+{
+    int ws = bits >> 5, bs = bits & 31;
+    Big r;
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        uint32_t lo = (i - ws >= 0) ? a.w[(i - ws) < 0 ? 0 : (i - ws)] : 0u;
+        uint32_t lo1 = (i - ws - 1 >= 0) ? a.w[(i - ws - 1) < 0 ? 0 : (i - ws - 1)] : 0u;
+        r.w[i] = bs ? ((lo << bs) | (lo1 >> (32 - bs))) : lo;
+    }
+    a = r;
+}
+
+__device__ __forceinline__ void big_shr1(Big &a)
+{
+#pragma unroll
+    for (int i = 0; i < NL - 1; i++) a.w[i] = (a.w[i] >> 1) | (a.w[i + 1] << 31);
+    a.w[NL - 1] >>= 1;
+}
+
+__device__ __forceinline__ int big_cmp(const Big &a, const Big &b)
+{
+    for (int i = NL - 1; i >= 0; i--) {
+        if (a.w[i] != b.w[i]) return a.w[i] > b.w[i] ? 1 : -1;
+    }
+    return 0;
+}
+
+__device__ __forceinline__ void big_sub(Big &a, const Big &b)
+{
+    uint32_t borrow = 0;
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        uint64_t t = (uint64_t)a.w[i] - b.w[i] - borrow;
+        a.w[i] = (uint32_t)t;
+        borrow = (uint32_t)(t >> 63);
+    }
+}
+
+__device__ __forceinline__ bool big_is_zero(const Big &a)
+{
+    uint32_t o = 0;
+#pragma unroll
+    for (int i = 0; i < NL; i++) o |= a.w[i];
+    return o == 0;
+}
+
+__device__ int big_bitlen(const Big &a)
+{
+    for (int i = NL - 1; i >= 0; i--)
+        if (a.w[i]) return i * 32 + (32 - __clz(a.w[i]));
+    return 0;
+}
+
+// floor(N / M) for a quotient known to be < 2^qbits; N becomes the remainder.
+__device__ uint64_t big_divq(Big &N, const Big &M, int qbits)
+{
+    Big T = M;
+    big_shl(T, qbits - 1);
+    uint64_t q = 0;
+    for (int i = qbits - 1; i >= 0; i--) {
+        if (big_cmp(N, T) >= 0) { big_sub(N, T); q |= 1ull << i; }
+        big_shr1(T);
+    }
+    return q;
+}
+
+// round-half-even of N/M given the floor q and the remainder R (in place of N)
+__device__ __forceinline__ uint64_t round_half_even(uint64_t q, Big &R, const Big &M)
+{
+    big_shl(R, 1);
+    int c = big_cmp(R, M);
+    if (c > 0 || (c == 0 && (q & 1))) q++;
+    return q;
+}
+
+// x > 0, finite, normal.  Returns D (10^11 <= D < 10^12), *k10 = decimal exponent of
+// the leading digit, *w12 = double nearest to D * 10^(k10 - 11).
+__device__ uint64_t g12(double x, int *k10, double *w12)
+{
+    int e2;
+    double fr = frexp(x, &e2);                 // x = fr * 2^e2, 0.5 <= fr < 1
+    uint64_t m = (uint64_t)ldexp(fr, 53);      // 53-bit integer
+    int e = e2 - 53;                           // x = m * 2^e
+    int k = (int)floor(log10(x));
+    uint64_t D = 0;
+    Big N, M;
+    for (int iter = 0; iter < 4; iter++) {
+        int q = k - 11;
+        big_set(N, m);
+        big_set(M, 1);
+        if (e >= 0) big_shl(N, e); else big_shl(M, -e);
+        if (q >= 0) big_mul_pow10(M, q); else big_mul_pow10(N, -q);
+        D = big_divq(N, M, 45);
+        if (D >= 1000000000000ull) { k++; continue; }
+        if (D < 100000000000ull) { k--; continue; }
+        break;
+    }
+    D = round_half_even(D, N, M);
+    if (D == 1000000000000ull) { D = 100000000000ull; k++; }
+    *k10 = k;
+    // ---- D * 10^q -> nearest double --------------------------------------
+    int q = k - 11;
+    big_set(N, D);
+    big_set(M, 1);
+    if (q >= 0) big_mul_pow10(N, q); else big_mul_pow10(M, -q);
+    int s = 53 - (big_bitlen(N) - big_bitlen(M));    // quotient of (N << s) / M has 53 or 54 bits
+    uint64_t Q = 0;
+    Big N2;
+    for (int iter = 0; iter < 2; iter++) {
+        N2 = N;
+        Big M2 = M;
+        if (s >= 0) big_shl(N2, s); else big_shl(M2, -s);
+        Q = big_divq(N2, M2, 55);
+        if (Q >= (1ull << 53)) { s--; continue; }
+        Q = round_half_even(Q, N2, M2);
+        break;
+    }
+    *w12 = ldexp((double)Q, -s);
+    return D;
+}
+
+__device__ __forceinline__ void g12_any(double x, int64_t *digits, int32_t *exp10, double *w12)
+{
+    if (x == 0.0 || !isfinite(x)) {   // 0 prints '0.0'; non-finite values cannot arise from count/norm
+        *digits = 0; *exp10 = 0; *w12 = x;
+        return;
+    }
+    double a = fabs(x), w;
+    if (a < 1e-30 || a > 1e30) {      // outside the 320-bit working range: flagged, the host refuses it
+        *digits = INT64_MIN; *exp10 = 0; *w12 = x;
+        return;
+    }
+    int k;
+    uint64_t D = g12(a, &k, &w);
+    *digits = x < 0 ? -(int64_t)D : (int64_t)D;
+    *exp10 = k;
+    *w12 = x < 0 ? -w : w;
+}
+
+__global__ void g12_kernel(const double *x, size_t n, int64_t *digits, int32_t *exp10, double *w12)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    g12_any(x[i], &digits[i], &exp10[i], &w12[i]);
+}
+
+// make_links.py:104-137,165-168
+__global__ void score_kernel(const uint64_t *keys, const uint64_t *counts, size_t n, uint32_t ncontig,
+                             const int64_t *re_left, const int64_t *re_right, double *score, uint8_t *is_int0,
+                             int64_t *digits, int32_t *exp10, double *w12, int32_t *u, int32_t *v)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t key = keys[i];
+    uint32_t ends = (uint32_t)(key & 3u);
+    uint64_t pr = key >> 2;
+    uint32_t first = (uint32_t)(pr / ncontig), second = (uint32_t)(pr % ncontig);
+    double x = (double)((ends & 2u) ? re_right[first] : re_left[first]);
+    double y = (double)((ends & 1u) ? re_right[second] : re_left[second]);
+    // r1 = (len/2)/len == 0.5 exactly for every non-zero finite length
+    double norm = __dadd_rn(__dmul_rn(x, 0.5), __dmul_rn(y, 0.5));
+    double s;
+    uint8_t int0 = 0;
+    if (norm == 0.0) { s = 0.0; int0 = 1; }                       // the int literal 0, :165-166
+    else s = __ddiv_rn(__dmul_rn((double)counts[i], 1.0), norm);  // :168
+    score[i] = s;
+    is_int0[i] = int0;
+    g12_any(s, &digits[i], &exp10[i], &w12[i]);
+    u[i] = (int32_t)(first * 2u + ((ends >> 1) & 1u));
+    v[i] = (int32_t)(second * 2u + (ends & 1u));
+}
+
+// ---- best-buddy: per-node top-2 with multiplicity ------------------------
+// weights are >= 0, so the IEEE bit pattern orders like the value
+__global__ void node_max_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, unsigned long long *nmax)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long b = (unsigned long long)__double_as_longlong(w[i]);
+    atomicMax(&nmax[u[i]], b);          // fast_scaled_scores.py:47-57
+    atomicMax(&nmax[v[i]], b);
+}
+
+__global__ void node_second_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n,
+                                   const unsigned long long *nmax, unsigned long long *nsecond, unsigned int *ntop)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long b = (unsigned long long)__double_as_longlong(w[i]);
+    int nd[2] = {u[i], v[i]};
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        if (b == nmax[nd[k]]) atomicAdd(&ntop[nd[k]], 1u);
+        else atomicMax(&nsecond[nd[k]], b);
+    }
+}
+
+__global__ void ratio_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, const unsigned long long *nmax,
+                             const unsigned long long *nsecond, const unsigned int *ntop, double *best_alt,
+                             uint8_t *is_int1, double *ratio, int64_t *digits, int32_t *exp10, int64_t *bdigits,
+                             int32_t *bexp10)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double wi = w[i];
+    int a = u[i], b = v[i];
+    double mu = __longlong_as_double((long long)nmax[a]), mv = __longlong_as_double((long long)nmax[b]);
+    double best = mu > mv ? mu : mv;                       // :79
+    if (best == wi) {                                      // :80-82  this edge is the best at both ends
+        // max over the OTHER edges at either end (get_max_weight, :13-33): the
+        // second-largest weight with multiplicity
+        double au = __longlong_as_double((long long)(ntop[a] >= 2 ? nmax[a] : nsecond[a]));
+        double av = __longlong_as_double((long long)(ntop[b] >= 2 ? nmax[b] : nsecond[b]));
+        best = au > av ? au : av;
+    }
+    uint8_t int1 = 0;
+    if (best == 0.0) { best = 1.0; int1 = 1; }             // :83-84  the int literal 1
+    best_alt[i] = best;
+    is_int1[i] = int1;
+    double r = __ddiv_rn(wi, best);                        // :86
+    ratio[i] = r;
+    double dummy;
+    g12_any(r, &digits[i], &exp10[i], &dummy);
+    g12_any(best, &bdigits[i], &bexp10[i], &dummy);     // text of column 4
+}
+
+__global__ void zero_nodes_kernel(unsigned long long *p, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = 0;
+}
+
+inline unsigned nblk(size_t n, int t) { return (unsigned)((n + t - 1) / t); }
+
+}   // namespace
+
+extern "C" int salsa_g12(const double *d_x, size_t n, int64_t *d_digits, int32_t *d_exp10, double *d_w12, void *stream)
+{
+    if (n == 0) return SALSA_OK;
+    if (!d_x || !d_digits || !d_exp10 || !d_w12) SALSA_FAIL(SALSA_ERR_ARG, "salsa_g12: NULL argument");
+    g12_kernel<<<nblk(n, 128), 128, 0, as_stream(stream)>>>(d_x, n, d_digits, d_exp10, d_w12);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
+extern "C" int salsa_links_score(const uint64_t *d_keys, const uint64_t *d_counts, size_t n, int32_t ncontig,
+                                 const int64_t *d_re_left, const int64_t *d_re_right, double *d_score, uint8_t *d_is_int0,
+                                 int64_t *d_digits, int32_t *d_exp10, double *d_w12, int32_t *d_u, int32_t *d_v, void *stream)
+{
+    if (n == 0) return SALSA_OK;
+    if (!d_keys || !d_counts || !d_re_left || !d_re_right || !d_score || !d_is_int0 || !d_digits || !d_exp10 || !d_w12 ||
+        !d_u || !d_v || ncontig <= 0)
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_links_score: bad argument");
+    score_kernel<<<nblk(n, 128), 128, 0, as_stream(stream)>>>(d_keys, d_counts, n, (uint32_t)ncontig, d_re_left, d_re_right,
+                                                              d_score, d_is_int0, d_digits, d_exp10, d_w12, d_u, d_v);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
+extern "C" size_t salsa_scaled_scratch_bytes(int32_t nnodes) { return (size_t)(nnodes > 0 ? nnodes : 0) * 24 + 64; }
+
+// scratch layout: nmax u64[nnodes] | nsecond u64[nnodes] | ntop u32[nnodes] (+pad)
+static int scaled_launch(const int32_t *d_u, const int32_t *d_v, const double *d_w, size_t n, int32_t nnodes,
+                         unsigned long long *nmax, double *d_best_alt, uint8_t *d_is_int1, double *d_ratio,
+                         int64_t *d_digits, int32_t *d_exp10, int64_t *d_bdigits, int32_t *d_bexp10, cudaStream_t st)
+{
+    unsigned long long *nsecond = nmax + nnodes;
+    unsigned int *ntop = (unsigned int *)(nsecond + nnodes);
+    size_t words = (size_t)nnodes * 2 + ((size_t)nnodes + 1) / 2;
+    zero_nodes_kernel<<<nblk(words, 256), 256, 0, st>>>(nmax, words);
+    node_max_kernel<<<nblk(n, 256), 256, 0, st>>>(d_u, d_v, d_w, n, nmax);
+    node_second_kernel<<<nblk(n, 256), 256, 0, st>>>(d_u, d_v, d_w, n, nmax, nsecond, ntop);
+    ratio_kernel<<<nblk(n, 128), 128, 0, st>>>(d_u, d_v, d_w, n, nmax, nsecond, ntop, d_best_alt, d_is_int1, d_ratio,
+                                               d_digits, d_exp10, d_bdigits, d_bexp10);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
+extern "C" int salsa_scaled_scores(const int32_t *d_u, const int32_t *d_v, const double *d_w, size_t n, int32_t nnodes,
+                                   void *d_scratch, double *d_best_alt, uint8_t *d_is_int1, double *d_ratio,
+                                   int64_t *d_ratio_digits, int32_t *d_ratio_exp10, int64_t *d_best_digits,
+                                   int32_t *d_best_exp10, void *stream)
+{
+    if (n == 0) return SALSA_OK;
+    if (!d_u || !d_v || !d_w || !d_scratch || !d_best_alt || !d_is_int1 || !d_ratio || !d_ratio_digits || !d_ratio_exp10 ||
+        !d_best_digits || !d_best_exp10 || nnodes <= 0)
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_scaled_scores: bad argument");
+    return scaled_launch(d_u, d_v, d_w, n, nnodes, (unsigned long long *)d_scratch, d_best_alt, d_is_int1, d_ratio,
+                         d_ratio_digits, d_ratio_exp10, d_best_digits, d_best_exp10, as_stream(stream));
+}
+
+// ---- host text assembly from (digits, exp10): Python-2 str(float) ---------
+static int fmt_g12(int64_t digits, int32_t k, char *out)
+{
+    char *p = out;
+    if (digits == 0) { memcpy(p, "0.0", 3); return 3; }
+    if (digits < 0) { *p++ = '-'; digits = -digits; }
+    char d[16];
+    int nd = 12;
+    for (int i = 11; i >= 0; i--) { d[i] = (char)('0' + digits % 10); digits /= 10; }
+    while (nd > 1 && d[nd - 1] == '0') nd--;          // %g strips trailing zeros
+    if (k < -4 || k >= 12) {                          // scientific
+        *p++ = d[0];
+        if (nd > 1) { *p++ = '.'; memcpy(p, d + 1, nd - 1); p += nd - 1; }
+        *p++ = 'e';
+        *p++ = k < 0 ? '-' : '+';
+        int a = k < 0 ? -k : k;
+        if (a >= 100) { *p++ = (char)('0' + a / 100); a %= 100; }
+        *p++ = (char)('0' + a / 10);
+        *p++ = (char)('0' + a % 10);
+    } else if (k >= 0) {
+        int ip = k + 1;                               // digits before the point
+        for (int i = 0; i < ip; i++) *p++ = i < nd ? d[i] : '0';
+        *p++ = '.';
+        if (nd > ip) { memcpy(p, d + ip, nd - ip); p += nd - ip; }
+        else *p++ = '0';                              // Python's '.0' for integral text
+    } else {
+        *p++ = '0'; *p++ = '.';
+        for (int i = 0; i < -k - 1; i++) *p++ = '0';
+        memcpy(p, d, nd); p += nd;
+    }
+    return (int)(p - out);
+}
+
+static inline char *put_i64(char *p, int64_t v)
+{
+    char t[24];
+    int n = 0;
+    bool neg = v < 0;
+    uint64_t a = neg ? (uint64_t)(-v) : (uint64_t)v;
+    do { t[n++] = (char)('0' + a % 10); a /= 10; } while (a);
+    if (neg) *p++ = '-';
+    while (n) *p++ = t[--n];
+    return p;
+}
+
+extern "C" int salsa_format_g12(const int64_t *h_digits, const int32_t *h_exp10, size_t n, char *h_out, size_t out_cap,
+                                int64_t *h_off)
+{
+    size_t pos = 0;
+    for (size_t i = 0; i < n; i++) {
+        if (pos + 32 > out_cap) SALSA_FAIL(SALSA_ERR_ARG, "salsa_format_g12: output buffer too small");
+        h_off[i] = (int64_t)pos;
+        pos += (size_t)fmt_g12(h_digits[i], h_exp10[i], h_out + pos);
+    }
+    h_off[n] = (int64_t)pos;
+    return SALSA_OK;
+}
+
+// contig_links_iteration_N: "first:X\tsecond:Y\tscore\tcount\n" (make_links.py:169)
+extern "C" int64_t salsa_format_links(const char *names_blob, const int64_t *name_off, const int64_t *first,
+                                      const int64_t *second, const uint8_t *ends, const int64_t *count,
+                                      const int64_t *digits, const int32_t *exp10, const uint8_t *is_int0, size_t n,
+                                      char *out, size_t out_cap)
+{
+    char *p = out;
+    for (size_t i = 0; i < n; i++) {
+        int64_t a = first[i], b = second[i];
+        size_t la = (size_t)(name_off[a + 1] - name_off[a]), lb = (size_t)(name_off[b + 1] - name_off[b]);
+        if ((size_t)(p - out) + la + lb + 80 > out_cap) { salsa_set_error("salsa_format_links: buffer too small"); return -1; }
+        memcpy(p, names_blob + name_off[a], la); p += la;
+        *p++ = ':'; *p++ = (ends[i] & 2) ? 'E' : 'B'; *p++ = '\t';
+        memcpy(p, names_blob + name_off[b], lb); p += lb;
+        *p++ = ':'; *p++ = (ends[i] & 1) ? 'E' : 'B'; *p++ = '\t';
+        if (is_int0[i]) *p++ = '0';
+        else p += fmt_g12(digits[i], exp10[i], p);
+        *p++ = '\t';
+        p = put_i64(p, count[i]);
+        *p++ = '\n';
+    }
+    return (int64_t)(p - out);
+}
+
+// contig_links_scaled_iteration_N (fast_scaled_scores.py:86):
+// u v str(w) str(bestAlt) str(w/bestAlt) links False False
+extern "C" int64_t salsa_format_scaled(const char *node_blob, const int64_t *node_off, const int32_t *u, const int32_t *v,
+                                       const int64_t *w_digits, const int32_t *w_exp10, const int64_t *b_digits,
+                                       const int32_t *b_exp10, const uint8_t *b_is_int1, const int64_t *r_digits,
+                                       const int32_t *r_exp10, const int64_t *links, size_t n, char *out, size_t out_cap)
+{
+    char *p = out;
+    for (size_t i = 0; i < n; i++) {
+        int64_t a = u[i], b = v[i];
+        size_t la = (size_t)(node_off[a + 1] - node_off[a]), lb = (size_t)(node_off[b + 1] - node_off[b]);
+        if ((size_t)(p - out) + la + lb + 140 > out_cap) { salsa_set_error("salsa_format_scaled: buffer too small"); return -1; }
+        memcpy(p, node_blob + node_off[a], la); p += la; *p++ = '\t';
+        memcpy(p, node_blob + node_off[b], lb); p += lb; *p++ = '\t';
+        p += fmt_g12(w_digits[i], w_exp10[i], p); *p++ = '\t';
+        if (b_is_int1[i]) *p++ = '1';
+        else p += fmt_g12(b_digits[i], b_exp10[i], p);
+        *p++ = '\t';
+        p += fmt_g12(r_digits[i], r_exp10[i], p); *p++ = '\t';
+        p = put_i64(p, links[i]);
+        memcpy(p, "\tFalse\tFalse\n", 13); p += 13;
+    }
+    return (int64_t)(p - out);
+}

@@ -158,6 +158,34 @@ class Engine:
         check(self.L.salsa_bed_ingest_dense_host(self.ctx, ptr, n, stage.data_ptr(), chunk_bytes,
                                                  self.table.data_ptr(), self.stats.data_ptr()))
 
+    def ingest_file(self, path, chunk_bytes=256 << 20):
+        """Ingest a BED file from disk (what make_links.py does with -b).  The file
+        is memory-mapped and streamed in line-aligned chunks that overlap by one
+        line (see salsa_bed_ingest_dense in include/salsa_b200.h)."""
+        import os
+        size = os.path.getsize(path)
+        if size == 0:
+            return
+        mm = np.memmap(path, dtype=np.uint8, mode='r')
+        if self.mode == 'dense' and not self.navoid:
+            self.ingest_host(mm, chunk_bytes=min(chunk_bytes, 64 << 20))
+            return
+        pos = 0
+        while pos < size:
+            end = min(pos + chunk_bytes, size)
+            nxt = size
+            if end < size:
+                blk = mm[pos:end]
+                nl = np.flatnonzero(blk[::-1][:4 * 1024 * 1024] == 10)      # newlines near the chunk's end
+                if len(nl) < 2:
+                    raise ValueError('BED line longer than the staging chunk near byte %d' % pos)
+                end = pos + (len(blk) - 1 - int(nl[0])) + 1
+                nxt = pos + (len(blk) - 1 - int(nl[1])) + 1
+            dev = torch.from_numpy(np.ascontiguousarray(mm[pos:end])).to(self.device)
+            self.ingest_device(dev, base_offset=pos)
+            torch.cuda.current_stream().synchronize()
+            pos = nxt
+
     def stats_read(self, raise_on_error=True):
         s = IngestStats()
         check(self.L.salsa_ingest_stats_read(self.stats.data_ptr(), C.byref(s), torch.cuda.current_stream().cuda_stream))
@@ -165,8 +193,8 @@ class Engine:
             raise DataError(s.err_code, s.err_offset)
         return s
 
-    def links(self):
-        """Compacted, key-sorted link list as numpy arrays (first, second, ends, count)."""
+    def _compact(self):
+        """(keys, counts, m): compacted, key-sorted link list on the device."""
         st = torch.cuda.current_stream().cuda_stream
         if self.mode == 'dense':
             kptr, cnt, ncell = None, self.table, self.table.numel()
@@ -189,10 +217,88 @@ class Engine:
             check(self.L.salsa_sort_pairs_u64(ok.data_ptr(), oc.data_ptr(), ok2.data_ptr(), oc2.data_ptr(), m, tmp.data_ptr(),
                                               C.byref(tb), st))
             ok, oc = ok2, oc2
+        return ok, oc, m
+
+    def _decode(self, ok, m):
         keys = ok[:m].cpu().numpy().astype(np.uint64)
-        counts = oc[:m].cpu().numpy()
         ends = (keys & np.uint64(3)).astype(np.uint8)
         pair = keys >> np.uint64(2)
         first = (pair // np.uint64(max(self.n, 1))).astype(np.int64)
         second = (pair % np.uint64(max(self.n, 1))).astype(np.int64)
-        return first, second, ends, counts
+        return first, second, ends
+
+    def links(self):
+        """Compacted, key-sorted link list as numpy arrays (first, second, ends, count)."""
+        ok, oc, m = self._compact()
+        first, second, ends = self._decode(ok, m)
+        return first, second, ends, oc[:m].cpu().numpy()
+
+    def score_links(self):
+        """make_links.py:161-169 on the device: per link the score, its str(float)
+        digits and the value float(str(score)) the next program sees."""
+        ok, oc, m = self._compact()
+        dev, st = self.device, torch.cuda.current_stream().cuda_stream
+        mm = max(m, 1)
+        rl = torch.from_numpy(self.re_left).to(dev)
+        rr = torch.from_numpy(self.re_right).to(dev)
+        score = torch.empty(mm, dtype=torch.float64, device=dev)
+        w12 = torch.empty(mm, dtype=torch.float64, device=dev)
+        int0 = torch.empty(mm, dtype=torch.uint8, device=dev)
+        digits = torch.empty(mm, dtype=torch.int64, device=dev)
+        exp10 = torch.empty(mm, dtype=torch.int32, device=dev)
+        u = torch.empty(mm, dtype=torch.int32, device=dev)
+        v = torch.empty(mm, dtype=torch.int32, device=dev)
+        check(self.L.salsa_links_score(ok.data_ptr(), oc.data_ptr(), m, self.n, rl.data_ptr(), rr.data_ptr(), score.data_ptr(),
+                                       int0.data_ptr(), digits.data_ptr(), exp10.data_ptr(), w12.data_ptr(), u.data_ptr(),
+                                       v.data_ptr(), st))
+        first, second, ends = self._decode(ok, m)
+        return dict(first=first, second=second, ends=ends, count=oc[:m].cpu().numpy(), score=score[:m].cpu().numpy(),
+                    is_int0=int0[:m].cpu().numpy(), digits=digits[:m].cpu().numpy(), exp10=exp10[:m].cpu().numpy(),
+                    w12=w12[:m], u=u[:m], v=v[:m], n=m)
+
+    def link_text(self, sc):
+        """contig_links_iteration_N content for a score_links() result (bytes)."""
+        blob, off = _blob(self.names)
+        cap = int(sc['n']) * 96 + 2 * int(off[-1] if len(off) else 0) + sum(0 for _ in ()) + 1024
+        cap += int((np.diff(off)[sc['first']].sum() + np.diff(off)[sc['second']].sum())) if sc['n'] else 0
+        out = C.create_string_buffer(cap)
+        f = np.ascontiguousarray(sc['first'], np.int64); s = np.ascontiguousarray(sc['second'], np.int64)
+        e = np.ascontiguousarray(sc['ends'], np.uint8); c = np.ascontiguousarray(sc['count'], np.int64)
+        d = np.ascontiguousarray(sc['digits'], np.int64); k = np.ascontiguousarray(sc['exp10'], np.int32)
+        z = np.ascontiguousarray(sc['is_int0'], np.uint8)
+        nb = self.L.salsa_format_links(blob, off.ctypes.data, f.ctypes.data, s.ctypes.data, e.ctypes.data, c.ctypes.data,
+                                       d.ctypes.data, k.ctypes.data, z.ctypes.data, int(sc['n']), out, cap)
+        if nb < 0:
+            check(-2)
+        return out.raw[:nb]
+
+    def g12(self, x):
+        """(digits, exp10, w12) of Python-2 str(float) for a float64 array (device kernel)."""
+        x = torch.as_tensor(np.ascontiguousarray(x, np.float64)).to(self.device)
+        n = x.numel()
+        d = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        k = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
+        w = torch.empty(max(n, 1), dtype=torch.float64, device=self.device)
+        check(self.L.salsa_g12(x.data_ptr(), n, d.data_ptr(), k.data_ptr(), w.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        return d[:n].cpu().numpy(), k[:n].cpu().numpy(), w[:n].cpu().numpy()
+
+    def scaled_scores(self, u, v, w, nnodes):
+        """fast_scaled_scores.py:35-89 on the device.  u, v int32 node ids, w float64
+        (device tensors or numpy).  Returns dict of numpy arrays."""
+        dev, st = self.device, torch.cuda.current_stream().cuda_stream
+        u = torch.as_tensor(u).to(dev, torch.int32).contiguous()
+        v = torch.as_tensor(v).to(dev, torch.int32).contiguous()
+        w = torch.as_tensor(w).to(dev, torch.float64).contiguous()
+        m = u.numel()
+        mm = max(m, 1)
+        scratch = torch.empty(self.L.salsa_scaled_scratch_bytes(nnodes) // 8 + 1, dtype=torch.int64, device=dev)
+        best = torch.empty(mm, dtype=torch.float64, device=dev)
+        int1 = torch.empty(mm, dtype=torch.uint8, device=dev)
+        ratio = torch.empty(mm, dtype=torch.float64, device=dev)
+        rd = torch.empty(mm, dtype=torch.int64, device=dev); rk = torch.empty(mm, dtype=torch.int32, device=dev)
+        bd = torch.empty(mm, dtype=torch.int64, device=dev); bk = torch.empty(mm, dtype=torch.int32, device=dev)
+        check(self.L.salsa_scaled_scores(u.data_ptr(), v.data_ptr(), w.data_ptr(), m, nnodes, scratch.data_ptr(), best.data_ptr(),
+                                         int1.data_ptr(), ratio.data_ptr(), rd.data_ptr(), rk.data_ptr(), bd.data_ptr(),
+                                         bk.data_ptr(), st))
+        g = lambda t: t[:m].cpu().numpy()   # noqa: E731
+        return dict(best_alt=g(best), is_int1=g(int1), ratio=g(ratio), r_digits=g(rd), r_exp10=g(rk), b_digits=g(bd), b_exp10=g(bk))

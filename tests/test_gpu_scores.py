@@ -1,0 +1,144 @@
+"""GPU parity tests: str(float) round trip, link scores, best-buddy ratios, and the
+drop-in make_links.py / fast_scaled_scores.py scripts against the oracle."""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, 'salsa_b200', 'bin')
+
+
+@pytest.fixture(scope='module')
+def eng():
+    sys.path.insert(0, BIN)
+    from _common import engine
+    return engine()
+
+
+def fmt(eng, digits, exp10):
+    import ctypes as C
+    n = len(digits)
+    out = C.create_string_buffer(n * 32 + 32)
+    off = np.zeros(n + 1, np.int64)
+    d = np.ascontiguousarray(digits, np.int64)
+    k = np.ascontiguousarray(exp10, np.int32)
+    assert eng.L.salsa_format_g12(d.ctypes.data, k.ctypes.data, n, out, n * 32 + 32, off.ctypes.data) == 0
+    raw = out.raw
+    return [raw[off[i]:off[i + 1]].decode() for i in range(n)]
+
+
+def test_g12_matches_python2_str(eng, oracle_lib):
+    rng = np.random.default_rng(7)
+    xs = list(np.exp(rng.uniform(np.log(1e-17), np.log(2e19), 200000)))
+    xs += [10.0 ** k for k in range(-17, 20)] + [10.0 ** k * (1 - 2 ** -53) for k in range(-17, 20)]
+    xs += [100000000000.5, 100000000001.5, 999999999999.5, 99999999999.95, 0.5, 0.25, 1 / 3.0, 2 / 3.0, 21659 / 210.0,
+           3 / 14.0, 123456789012.0, 1234567890123.0, 0.0001, 0.00001, 9.9999999999995e-5, 1e22, 3e-29, 7e29,
+           0.0, -2.5, -1 / 3.0]
+    xs += [c / (a * 0.5 + b * 0.5) for a, b, c in rng.integers(1, 5000, (50000, 3))]
+    x = np.array(xs, dtype=np.float64)
+    d, k, w = eng.g12(x)
+    txt = fmt(eng, d, k)
+    for i in range(0, len(x), 1):
+        want = oracle_lib.py2_str_float(float(x[i])) if i % 17 == 0 or i > 200000 else None
+        if want is not None:
+            assert txt[i] == want, (x[i], txt[i], want)
+    # vectorised check of every element against Python's own formatting
+    want_all = ['%.12g' % v for v in x]
+    want_all = [s if ('.' in s or 'e' in s or 'n' in s) else s + '.0' for s in want_all]
+    assert txt == want_all
+    assert (w == np.array([float(s) for s in want_all])).all()
+
+
+def _case(seed, ncontig=40, npairs=20000):
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=ncontig, genome=20000 * ncontig, npairs=npairs, seed=seed, triple=0.02, noise=0.15)
+    rng = np.random.default_rng(seed)
+    rl = rng.integers(0, 60, ncontig)
+    rr = rng.integers(0, 60, ncontig)
+    rl[:3] = 0
+    rr[:3] = 0          # norm == 0 -> the int literal 0
+    return asm, bed, rl, rr
+
+
+def _write_dir(d, asm, bed, rl, rr, it=1):
+    open(d + '/scaffold_length_iteration_%d' % it, 'wb').write(asm.lengths_text())
+    open(d + '/re_counts_iteration_%d' % it, 'wb').write(b''.join(b'%s %d %d\n' % (n, a, b) for n, a, b in zip(asm.names, rl, rr)))
+    open(d + '/b.bed', 'wb').write(bed)
+
+
+@pytest.mark.parametrize('seed', [1, 2])
+def test_dropin_scripts_match_oracle(eng, oracle_lib, seed):
+    import make_links
+    import fast_scaled_scores
+    asm, bed, rl, rr = _case(seed)
+    dg, do = tempfile.mkdtemp(), tempfile.mkdtemp()
+    for d in (dg, do):
+        _write_dir(d, asm, bed, rl, rr)
+    assert make_links.main(['-b', dg + '/b.bed', '-d', dg, '-i', '1', '-x', 'abc']) == 0
+    oracle_lib.make_links_files(do + '/b.bed', do, 1)
+    a = open(dg + '/contig_links_iteration_1', 'rb').read()
+    b = open(do + '/contig_links_iteration_1', 'rb').read()
+    assert a == b and len(a) > 1000
+    assert b'\t0\t' in a                     # a norm == 0 link is present and printed as the int 0
+    assert fast_scaled_scores.main(['-d', dg, '-i', '1']) == 0
+    oracle_lib.fast_scaled_scores_files(do, 1)
+    a = open(dg + '/contig_links_scaled_iteration_1', 'rb').read()
+    b = open(do + '/contig_links_scaled_iteration_1', 'rb').read()
+    assert a == b
+    env = dict(os.environ, LC_ALL='C')
+    sa = subprocess.run(['sort', '-k', '5', '-gr', dg + '/contig_links_scaled_iteration_1'], capture_output=True, env=env).stdout
+    sb = subprocess.run(['sort', '-k', '5', '-gr', do + '/contig_links_scaled_iteration_1'], capture_output=True, env=env).stdout
+    assert sa == sb
+
+
+def test_scaled_kats(eng, oracle_lib):
+    import fast_scaled_scores
+    cases = [
+        ['a:B\tb:B\t4.0\t7\n', 'a:B\tc:B\t2.0\t3\n'],
+        ['a:B\tb:B\t3.5\t7\n', 'c:E\td:B\t0\t1\n'],
+        ['a:B\tb:B\t2.0\t1\n', 'a:B\tc:B\t2.0\t1\n'],
+        ['a:B\tb:B\t2.0\t1\n', 'a:B\tc:B\t2.0\t1\n', 'a:B\td:E\t2.0\t9\n', 'b:B\td:E\t0.5\t2\n'],
+        ['x:E\ty:B\t103.138095238\t21659\n', 'x:E\tz:B\t0.214285714286\t1\n', 'y:B\tz:B\t1e-05\t1\n'],
+    ]
+    rng = np.random.default_rng(3)
+    big = []
+    for i in range(300):
+        for j in rng.choice(300, 4, replace=False):
+            if i < j:
+                big.append('n%d:%s\tn%d:%s\t%s\t%d\n' % (i, 'BE'[i % 2], j, 'BE'[j % 2],
+                                                     oracle_lib.py2_str_float(float(rng.integers(0, 40)) / float(rng.integers(1, 9))),
+                                                     rng.integers(1, 500)))
+    cases.append(big)
+    for lines in cases:
+        want = ''.join(oracle_lib.scaled_lines_from_link_lines(lines)).encode()
+        got = fast_scaled_scores.scaled_text(eng, [ln.encode() for ln in lines])
+        assert got == want
+
+
+def test_kat_link_score_line(eng):
+    # KAT-links: A:B  B:E  0.285714285714  1
+    import make_links
+    d = tempfile.mkdtemp()
+    open(d + '/scaffold_length_iteration_1', 'w').write('A\t1000\nB\t2000\n')
+    open(d + '/re_counts_iteration_1', 'w').write('A 3 5\nB 2 4\n')
+    open(d + '/b.bed', 'w').write('A 100 200 r1/1\nB 1900 1990 r1/2\n')
+    assert make_links.main(['-b', d + '/b.bed', '-d', d, '-i', '1']) == 0
+    assert open(d + '/contig_links_iteration_1').read() == 'A:B\tB:E\t0.285714285714\t1\n'
+
+
+def test_make_links_fails_like_reference(eng):
+    import make_links
+    from salsa_b200.engine import DataError
+    d = tempfile.mkdtemp()
+    open(d + '/scaffold_length_iteration_1', 'w').write('A\t1000\n')
+    open(d + '/re_counts_iteration_1', 'w').write('A 3 5\n')
+    open(d + '/b.bed', 'w').write('A 100 200 r1/1\nB 1900 1990 r1/2\n')
+    with pytest.raises(DataError):
+        make_links.main(['-b', d + '/b.bed', '-d', d, '-i', '1'])
+    assert not os.path.exists(d + '/contig_links_iteration_1')
