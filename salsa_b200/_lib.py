@@ -55,7 +55,7 @@ SIGNATURES = {
     'salsa_links_compact': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_u64), c_void_p]),
     'salsa_sort_pairs_u64': (C.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_size_t), c_void_p]),
     'salsa_g12': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_void_p]),
-    'salsa_links_score': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 11),
+    'salsa_links_score': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 10),
     'salsa_scaled_scratch_bytes': (c_size_t, [c_i32]),
     'salsa_scaled_scores': (C.c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 9),
     'salsa_format_g12': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
