@@ -219,6 +219,39 @@ int salsa_scaled_scores(const int32_t *d_u, const int32_t *d_v, const double *d_
                         int32_t *d_best_exp10, void *stream);
 
 /*
+ * salsa_scaled_scores for callers that cannot allocate.  (No counterpart in
+ * the reference: this entry point exists for the hosts of this library, not
+ * for parity with a reference function.)
+ *
+ * Who needs it: code that is handed only its input and output buffers and has
+ * no way to come up with a device scratch buffer at call time -- e.g. a plugin
+ * called inside a host program's stream-ordered section where cudaMalloc (a
+ * device-wide synchronising call) is forbidden, a pipeline stage whose memory
+ * pool is frozen while it runs, or a minimal cgo/JNI-style binding that has no
+ * allocator on the device side.  Same inputs, outputs and results as
+ * salsa_scaled_scores; the per-node working arrays live in a fixed array that
+ * is part of the loaded library image.
+ *
+ *   - Limit: nnodes <= salsa_scaled_scores_static_max_nodes() (65536 contig
+ *     ends = 32768 contigs); more is rejected with SALSA_ERR_ARG and a message
+ *     that names the limit.  The array is about 1.5 MB and stays resident on
+ *     every GPU that loads the library until the process exits.
+ *   - Calls cudaMalloc / cudaFree / any allocating routine: never.
+ *   - The first call on each device looks up the array's device address (a
+ *     one-time, per-device set-up done with that device current).  Make that
+ *     first call before starting any stream capture on that device.
+ *   - All calls on a device share the one array.  Its contents after a call
+ *     are leftovers; each call clears what it needs before use.  Two calls
+ *     whose kernels can overlap on the GPU (different streams, or different
+ *     host threads without ordering) race on it: serialise them.
+ */
+int32_t salsa_scaled_scores_static_max_nodes(void);
+int salsa_scaled_scores_static(const int32_t *d_u, const int32_t *d_v, const double *d_w, size_t n, int32_t nnodes,
+                               double *d_best_alt, uint8_t *d_is_int1, double *d_ratio,
+                               int64_t *d_ratio_digits, int32_t *d_ratio_exp10, int64_t *d_best_digits,
+                               int32_t *d_best_exp10, void *stream);
+
+/*
  * Host-side text assembly (no float conversion happens here: text is built
  * from the integer digits the device produced).
  * salsa_format_g12   : str(float) strings, concatenated; h_off[n+1] offsets

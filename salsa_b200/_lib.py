@@ -58,6 +58,8 @@ SIGNATURES = {
     'salsa_links_score': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 10),
     'salsa_scaled_scratch_bytes': (c_size_t, [c_i32]),
     'salsa_scaled_scores': (C.c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 9),
+    'salsa_scaled_scores_static_max_nodes': (c_i32, []),
+    'salsa_scaled_scores_static': (C.c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 8),
     'salsa_format_g12': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
     'salsa_format_links': (c_i64, [C.c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_size_t, c_void_p, c_size_t]),

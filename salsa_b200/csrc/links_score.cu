@@ -13,6 +13,8 @@
 // (round-half-even on the exact binary value, like glibc/CPython) and the
 // correctly rounded double of D*10^(k-11).  The host only assembles text from
 // (D, k); it never converts a float.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -339,6 +341,64 @@ extern "C" int salsa_scaled_scores(const int32_t *d_u, const int32_t *d_v, const
         !d_best_digits || !d_best_exp10 || nnodes <= 0)
         SALSA_FAIL(SALSA_ERR_ARG, "salsa_scaled_scores: bad argument");
     return scaled_launch(d_u, d_v, d_w, n, nnodes, (unsigned long long *)d_scratch, d_best_alt, d_is_int1, d_ratio,
+                         d_ratio_digits, d_ratio_exp10, d_best_digits, d_best_exp10, as_stream(stream));
+}
+
+// ---- best-buddy ratios for callers that must not allocate -----------------
+// Some hosts of this library cannot obtain device memory at call time: a
+// plugin running inside another program's stream-ordered section, a caller
+// whose memory pool is frozen for the duration of a pipeline stage, or a
+// thin FFI binding (cgo / JNI style) that is only handed input and output
+// buffers and has no allocator of its own to produce a scratch buffer.  For
+// them the per-node working arrays live in this fixed device array instead of
+// a caller-provided buffer.  It is part of the loaded module, so every GPU
+// that loads libsalsa_b200 holds these bytes until the process exits.
+#define SALSA_STATIC_MAX_NODES 65536
+static __device__ __align__(256) unsigned char g_scaled_scratch[(size_t)SALSA_STATIC_MAX_NODES * 24 + 256];
+
+// In host code `g_scaled_scratch` is only a handle for the symbol, not a
+// device address; the address a kernel can use is looked up once per device.
+static std::mutex g_static_mu;
+static void *g_static_ptr[64];
+
+static int static_scratch_ptr(void **out)
+{
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) SALSA_FAIL(SALSA_ERR_UNSUPPORTED, "device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void *p = NULL;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_scaled_scratch));   // resolved on the CURRENT device
+        if (!p) SALSA_FAIL(SALSA_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return SALSA_OK;
+}
+
+extern "C" int32_t salsa_scaled_scores_static_max_nodes(void) { return SALSA_STATIC_MAX_NODES; }
+
+extern "C" int salsa_scaled_scores_static(const int32_t *d_u, const int32_t *d_v, const double *d_w, size_t n,
+                                          int32_t nnodes, double *d_best_alt, uint8_t *d_is_int1, double *d_ratio,
+                                          int64_t *d_ratio_digits, int32_t *d_ratio_exp10, int64_t *d_best_digits,
+                                          int32_t *d_best_exp10, void *stream)
+{
+    if (nnodes > SALSA_STATIC_MAX_NODES)
+        SALSA_FAIL(SALSA_ERR_ARG,
+                   "salsa_scaled_scores_static: %d nodes exceed the built-in scratch limit of %d nodes "
+                   "(use salsa_scaled_scores with a caller-provided scratch buffer)",
+                   nnodes, SALSA_STATIC_MAX_NODES);
+    if (n == 0) return SALSA_OK;
+    if (!d_u || !d_v || !d_w || !d_best_alt || !d_is_int1 || !d_ratio || !d_ratio_digits || !d_ratio_exp10 ||
+        !d_best_digits || !d_best_exp10 || nnodes <= 0)
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_scaled_scores_static: bad argument");
+    void *scratch = NULL;
+    int rc = static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    // scaled_launch zeroes the node arrays it uses before the first atomic, so
+    // whatever the previous call left behind is never read.
+    return scaled_launch(d_u, d_v, d_w, n, nnodes, (unsigned long long *)scratch, d_best_alt, d_is_int1, d_ratio,
                          d_ratio_digits, d_ratio_exp10, d_best_digits, d_best_exp10, as_stream(stream));
 }
 
