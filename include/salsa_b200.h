@@ -252,6 +252,54 @@ int salsa_scaled_scores_static(const int32_t *d_u, const int32_t *d_v, const dou
                                int32_t *d_best_exp10, void *stream);
 
 /*
+ * Restriction-site counting.  Replaces RE_sites.py:6-28 (parse_fasta) and
+ * RE_sites.py:45-88 (per contig, per expanded enzyme pattern, the starts of
+ * non-overlapping re.finditer matches, split at len/2).  The FASTA text is in
+ * device memory; record names are read by the host from the header lines.
+ *
+ *  1. salsa_fasta_headers: byte offsets of every '>' that starts a line
+ *     (RE_sites.py:11), unordered; *d_count may exceed `capacity` (then retry
+ *     with a larger buffer).
+ *  2. The host sorts them, reads the header lines and forms the sequence
+ *     spans [beg, end) = text between a header line's '\n' and the next header.
+ *  3. salsa_fasta_count: per 4 KiB text tile (salsa_fasta_tiles(nbytes) tiles)
+ *     the number of KEPT bytes: bytes of a span that are not '\n' and not
+ *     trailing whitespace of their line (ln.rstrip(), RE_sites.py:22).
+ *     salsa_exclusive_scan_u64 turns d_tile_cnt[tiles + 1] into offsets.
+ *  4. salsa_fasta_span_lengths: kept-byte prefix at each span's start
+ *     (d_pbeg) and the span's sequence length (d_plen = len(seq)).
+ *  5. salsa_fasta_pack: sequences -> bit planes.  Record r starts at 64-base
+ *     block d_blk_off[r] (blocks = ceil(len/64), caller-computed prefix,
+ *     nspan + 1 entries); block b holds three uint64: hi, lo, valid with
+ *     A=00 C=01 G=10 T=11 and valid=0 for every other character (sequence N,
+ *     lower case and stray bytes never match, RE_sites.py:66).  d_planes must
+ *     be zeroed by the caller (3 * nblk uint64).
+ *  6. salsa_re_count: all patterns in one pass.  `patterns` = npat expanded
+ *     patterns ([ACGT]+, each <= 63 chars, NUL-terminated, concatenated; the
+ *     N expansion of RE_sites.py:52-56 is done by the host; a pattern listed
+ *     twice counts twice).  d_left/d_right: uint64 [nrec], ADDED to.
+ *     d_occ_scratch: nblk uint64 per self-overlapping pattern (e.g. AAAA), may
+ *     be NULL when no pattern overlaps itself.
+ * d_err (int32, caller-zeroed) becomes non-zero when a run of trailing
+ * whitespace longer than 1024 bytes is met (library limit).
+ */
+int salsa_fasta_headers(const void *d_fasta, size_t nbytes, uint64_t *d_pos, uint32_t *d_count, uint32_t capacity,
+                        void *stream);
+size_t salsa_fasta_tiles(size_t nbytes);
+int salsa_fasta_count(const void *d_fasta, size_t nbytes, const uint64_t *d_span_beg, const uint64_t *d_span_end,
+                      int32_t nspan, uint64_t *d_tile_cnt, int32_t *d_err, void *stream);
+int salsa_exclusive_scan_u64(uint64_t *d_vals, size_t n, void *stream);
+int salsa_fasta_span_lengths(const void *d_fasta, size_t nbytes, const uint64_t *d_span_beg,
+                             const uint64_t *d_span_end, int32_t nspan, const uint64_t *d_tile_excl,
+                             uint64_t *d_pbeg, uint64_t *d_plen, int32_t *d_err, void *stream);
+int salsa_fasta_pack(const void *d_fasta, size_t nbytes, const uint64_t *d_span_beg, const uint64_t *d_span_end,
+                     int32_t nspan, const uint64_t *d_tile_excl, const uint64_t *d_pbeg, const uint64_t *d_blk_off,
+                     uint64_t *d_planes, int32_t *d_err, void *stream);
+int salsa_re_count(const uint64_t *d_planes, const uint64_t *d_blk_off, const uint64_t *d_seqlen, int32_t nrec,
+                   uint64_t nblk, const char *patterns, int32_t npat, uint64_t *d_left, uint64_t *d_right,
+                   uint64_t *d_occ_scratch, void *stream);
+
+/*
  * Host-side text assembly (no float conversion happens here: text is built
  * from the integer digits the device produced).
  * salsa_format_g12   : str(float) strings, concatenated; h_off[n+1] offsets

@@ -60,6 +60,16 @@ SIGNATURES = {
     'salsa_scaled_scores': (C.c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 9),
     'salsa_scaled_scores_static_max_nodes': (c_i32, []),
     'salsa_scaled_scores_static': (C.c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 8),
+    'salsa_fasta_headers': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, C.c_uint32, c_void_p]),
+    'salsa_fasta_tiles': (c_size_t, [c_size_t]),
+    'salsa_fasta_count': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p]),
+    'salsa_exclusive_scan_u64': (C.c_int, [c_void_p, c_size_t, c_void_p]),
+    'salsa_fasta_span_lengths': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p,
+                                           c_void_p, c_void_p]),
+    'salsa_fasta_pack': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p]),
+    'salsa_re_count': (C.c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_u64, C.c_char_p, c_i32, c_void_p, c_void_p,
+                                 c_void_p, c_void_p]),
     'salsa_format_g12': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
     'salsa_format_links': (c_i64, [C.c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_size_t, c_void_p, c_size_t]),

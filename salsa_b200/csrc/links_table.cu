@@ -109,6 +109,15 @@ __global__ void __launch_bounds__(CT) write_kernel(const uint64_t *keys, const u
 
 }   // namespace
 
+// in-place exclusive scan of d_vals[0..n); the total lands in d_vals[n]
+extern "C" int salsa_exclusive_scan_u64(uint64_t *d_vals, size_t n, void *stream)
+{
+    if (!d_vals) SALSA_FAIL(SALSA_ERR_ARG, "salsa_exclusive_scan_u64: NULL argument");
+    scan_kernel<<<1, 1024, 0, as_stream(stream)>>>(d_vals, n);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
 extern "C" size_t salsa_links_compact_scratch_bytes(size_t ncells)
 {
     size_t nb = (ncells + CHUNK - 1) / CHUNK;
