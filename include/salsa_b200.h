@@ -300,6 +300,73 @@ int salsa_re_count(const uint64_t *d_planes, const uint64_t *d_blk_off, const ui
                    uint64_t *d_occ_scratch, void *stream);
 
 /*
+ * Hi-C physical coverage for misassembly detection.
+ * Replaces break_contigs_start.cpp:307-460 (run once with -m yes,
+ * run_pipeline.py:120-121) and break_contigs.cpp:199-356 (every iteration,
+ * run_pipeline.py:222-230,327-335).
+ *
+ * Step 1, BED scan -> coverage difference arrays (one pass over the BED text,
+ * same chunking rule as salsa_bed_ingest_dense: chunks overlap by one line):
+ *   contig table: salsa_names_build with h_len_floor = the length read as
+ *       `long` (break_contigs_start.cpp:286-294); d_len holds the same values
+ *       by contig id on the device.
+ *   d_covoff[id] : element offset of that contig's int32 difference array
+ *       (len + 10 elements, break_contigs_start.cpp:335) inside d_diff, or
+ *       UINT64_MAX for contigs shorter than 1,000,000 (never analysed, :325).
+ *   d_diff       : zeroed by the caller; diff[span_start] += 1,
+ *       diff[span_end + 1] -= 1 per accepted read pair (:375-376 / :242-243).
+ *   d_touched[id]: set to 1 when any line lands on an analysed contig (the
+ *       reference creates its coverage vector then, :333-337).
+ *   first_chunk  : non-zero when d_bed starts at the FIRST line of the file:
+ *       the reference never parses that line, so the pair (line 0, line 1) is
+ *       not evaluated (:315-319).
+ *   joins variant: d_join_off[n+1] / d_join_pos = CSR of the KEPT join
+ *       positions per scaffold (pos - 2,000,000 >= 0 and pos + 2,000,000 <= len,
+ *       break_contigs.cpp:84-87), ascending; a pair counts only when
+ *       prev_end <= start and [prev_start, end + 1] lies inside some join's
+ *       +-2 Mb window (:235-238).
+ * Data conditions reported through d_stats (salsa_ingest_stats):
+ *   SALSA_DATA_MALFORMED: a line on which `iss >> contig >> start >> end >>
+ *       read` fails; the reference's loop stops there (:321-322 / :212-213), so
+ *       the caller must zero d_diff / d_touched and rescan the first
+ *       err_offset bytes only.
+ *   SALSA_DATA_RANGE: an index the reference's vector::at() would reject
+ *       (it aborts).
+ *
+ * Step 2, salsa_cov_analyse: for each segment an inclusive prefix sum of the
+ * difference values (coverage), its exact integer total, and for the 11
+ * thresholds cutoff = (total/len)/div, div = 5..15, the [start, end] of
+ * Kadane's maximum-sum window over delta = (cov < cutoff ? +5 : -5) restricted
+ * to [lo, hi), with the reference's tie rules (break_contigs_start.cpp:412-449,
+ * break_contigs.cpp:298-335).  A segment is a whole contig (src_off ==
+ * dst_off: in place; lo = sz/100, hi = 9*sz/10, sz = len + 10) or the window
+ * [pos - 2 Mb, pos + 2 Mb) of a join (seed_idx = index of diff[start - 1], the
+ * RAW difference value the reference seeds its local prefix with,
+ * break_contigs.cpp:283-285; dst in a separate buffer; lo = sz/3, hi = 2*sz/3).
+ * h_start/h_end: [nseg * 11], relative to the segment.  Synchronises.
+ */
+#define SALSA_DATA_MALFORMED 7
+#define SALSA_DATA_RANGE 8
+typedef struct {
+    uint64_t src_off;   /* first element in d_diff */
+    uint64_t dst_off;   /* first element in d_cov */
+    uint64_t seed_idx;  /* element of d_diff added before the first element; UINT64_MAX = none */
+    int64_t len;        /* elements */
+    int64_t lo, hi;     /* Kadane range [lo, hi) */
+} salsa_cov_seg;
+int salsa_cov_scan_start(salsa_ctx *ctx, const void *d_bed, size_t nbytes, uint64_t base_offset, int32_t first_chunk,
+                         const uint64_t *d_covoff, const int64_t *d_len, int32_t *d_diff, uint8_t *d_touched,
+                         uint64_t *d_stats, void *stream);
+int salsa_cov_scan_joins(salsa_ctx *ctx, const void *d_bed, size_t nbytes, uint64_t base_offset, int32_t first_chunk,
+                         const uint64_t *d_covoff, const int64_t *d_len, const uint64_t *d_join_off,
+                         const int64_t *d_join_pos, int32_t *d_diff, uint8_t *d_touched, uint64_t *d_stats,
+                         void *stream);
+size_t salsa_cov_scratch_bytes(const salsa_cov_seg *h_segs, int32_t nseg);
+int salsa_cov_analyse(const int32_t *d_diff, int32_t *d_cov, const salsa_cov_seg *h_segs, int32_t nseg,
+                      void *d_scratch, size_t scratch_bytes, int64_t *h_sum, int64_t *h_start, int64_t *h_end,
+                      void *stream);
+
+/*
  * Host-side text assembly (no float conversion happens here: text is built
  * from the integer digits the device produced).
  * salsa_format_g12   : str(float) strings, concatenated; h_off[n+1] offsets

@@ -235,6 +235,18 @@ def cov_joins(bed, names, lengths, breakpoints):
     return rows, tot.value, sus.value
 
 
+def cov_analyse(diff, seed, lo, hi):
+    """Prefix + total + the 11 Kadane windows of one segment (oracle_cov_analyse)."""
+    L = lib()
+    diff = np.ascontiguousarray(diff, dtype=np.int32)
+    s = C.c_int64(0)
+    st = np.zeros(11, np.int64)
+    en = np.zeros(11, np.int64)
+    _check(L.oracle_cov_analyse(_p(diff, C.c_int32), C.c_int64(len(diff)), C.c_int32(seed), C.c_int64(lo), C.c_int64(hi),
+                                C.byref(s), _p(st, C.c_int64), _p(en, C.c_int64)))
+    return s.value, st, en
+
+
 # ---------------------------------------------------------------------------
 # file-level helpers: the same argv/file contract as the reference programs
 # ---------------------------------------------------------------------------

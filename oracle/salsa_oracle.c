@@ -983,3 +983,26 @@ int oracle_cov_joins(const char *bed, size_t nbytes, int32_t ncontig, const char
     free(local); free(cov); sm_free(&names);
     return ORC_OK;
 }
+
+/*
+ * oracle_cov_analyse: the per-segment arithmetic shared by both coverage
+ * programs, exposed so tests can hammer the tie rules on small arrays:
+ * inclusive prefix (seeded), exact total, and the 11 Kadane windows on
+ * [lo,hi) -- the same kadane() the two restatements above use
+ * (break_contigs_start.cpp:397-449, break_contigs.cpp:283-335).
+ */
+int oracle_cov_analyse(const int32_t *diff, int64_t len, int32_t seed, int64_t lo, int64_t hi,
+                       int64_t *out_sum, int64_t *out_start, int64_t *out_end)
+{
+    int32_t *cov = malloc((size_t)(len + 1) * sizeof(int32_t));
+    if (!cov) FAIL(ORC_NOMEM, "out of memory");
+    int32_t run = seed;
+    double sum = 0;
+    for (int64_t i = 0; i < len; i++) { run += diff[i]; cov[i] = run; sum += (double)run; }
+    *out_sum = (int64_t)sum;
+    double average = sum / (double)len;
+    for (int div = 5; div <= 15; div++)
+        kadane(cov, lo, hi, average / div, lo, lo, &out_start[div - 5], &out_end[div - 5]);
+    free(cov);
+    return ORC_OK;
+}

@@ -70,6 +70,13 @@ SIGNATURES = {
                                    c_void_p, c_void_p]),
     'salsa_re_count': (C.c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_u64, C.c_char_p, c_i32, c_void_p, c_void_p,
                                  c_void_p, c_void_p]),
+    'salsa_cov_scan_start': (C.c_int, [c_void_p, c_void_p, c_size_t, c_u64, c_i32, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p]),
+    'salsa_cov_scan_joins': (C.c_int, [c_void_p, c_void_p, c_size_t, c_u64, c_i32, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_void_p, c_void_p]),
+    'salsa_cov_scratch_bytes': (c_size_t, [c_void_p, c_i32]),
+    'salsa_cov_analyse': (C.c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p,
+                                    c_void_p]),
     'salsa_format_g12': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
     'salsa_format_links': (c_i64, [C.c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_size_t, c_void_p, c_size_t]),
