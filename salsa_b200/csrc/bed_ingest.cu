@@ -21,6 +21,9 @@ struct LinkArgs {
 template <bool SPARSE>
 struct LinkPolicy {
     typedef LinkArgs Args;
+    static constexpr bool NEED_RFULL = false;
+    // make_links.py:78 compares read.split('/')[0]
+    static __device__ __forceinline__ int read_cmp_len(int rslash, int /*rfull*/) { return rslash; }
 
     static __device__ __forceinline__ void emit(const LinkArgs &L, const ScanArgs &A, uint64_t key, uint64_t line_off)
     {
@@ -53,8 +56,7 @@ struct LinkPolicy {
         if (pnf < 1 || cnf < 1) { report(A.stats, line_off, SALSA_DATA_INDEX_ERROR); return false; }   // :71
         if (same_contig(s, pv, cu)) return false;
         if (pnf < 4 || cnf < 4) { report(A.stats, line_off, SALSA_DATA_INDEX_ERROR); return false; }   // :76-77
-        int pl = pv.read >> 16, cl = cu.read >> 16;
-        if (pl != cl || !bytes_equal_back(s, pv.read & 0xFFFF, cu.read & 0xFFFF, cl)) return false;    // :78
+        if (!reads_equal(s, pv, cu)) return false;                                                     // :78
         if ((pv.flags | cu.flags) & 8u) { report(A.stats, line_off, SALSA_DATA_VALUE_ERROR); return false; }  // :81-82
         if (pv.id < 0 || cu.id < 0) { report(A.stats, line_off, SALSA_DATA_KEY_ERROR); return false; }  // :101-102
         ContigMeta mp = A.t.meta[pv.id], mc = A.t.meta[cu.id];

@@ -10,11 +10,21 @@
 //   * a tile OWNS the lines whose first byte lies in (t0, t1]; it evaluates the
 //     adjacent-line pairs whose second line it owns, so every pair is
 //     evaluated exactly once and the line at offset 0 only ever plays "previous";
-//   * warps find newlines with an exact SWAR zero-byte test, 16 bytes per lane,
-//     and compact the line starts with a warp scan;
-//   * one thread parses one line from shared memory (first four fields) and
-//     hands its record to the next lane by warp shuffle -- the "previous line";
-//   * Policy::pair() decides what an adjacent pair contributes.
+//   * CLASSIFY (cooperative, 16 bytes per lane, exact SWAR byte tests + dp4a bit
+//     packing): a bitmap of "special" bytes (<= 0x20 or '/') for the whole staged
+//     region, and the newline positions of the owned region, compacted into the
+//     list of line starts (ballot rank; a general warp scan when a 16-byte chunk
+//     holds two newlines);
+//   * PARSE (one thread per line, branch-free fast path): the first four set
+//     bits of the special bitmap are the field boundaries; the contig name is
+//     looked up from a 16-byte unaligned window, start/end are converted 12
+//     digits at a time (xor 0x30, SWAR digit check, dp4a), the read name is
+//     packed into 8 words.  Anything the fast path cannot prove well-formed
+//     (odd whitespace, signs, long fields, '/' in a contig name ...) goes
+//     through the byte-loop parser parse_line(), which implements str.split()
+//     in full -- results are identical, only speed differs;
+//   * the record travels to the next lane by warp shuffle -- the "previous
+//     line" -- and Policy::pair() decides what the adjacent pair contributes.
 #pragma once
 #include "common.cuh"
 
@@ -28,6 +38,8 @@ constexpr int LCAP = 2048;             // line starts per scan range
 constexpr int WCAP = LCAP / NWARPS;    // per-warp segment
 constexpr int SUBTILE = 2048;          // fallback range: <= 2048 line starts by construction
 constexpr int SMEM_BYTES = HALO + TILE + HALO + 32;
+constexpr int SPWORDS = SMEM_BYTES / 32 + 4;   // special-byte bitmap, 1 bit per staged byte (+ guard words)
+constexpr int RW = 8;                  // read-name words carried per record (32 bytes)
 
 struct ScanArgs {
     const uint8_t *abase;     // 16-byte aligned base (<= caller pointer)
@@ -43,9 +55,21 @@ struct Rec {
     int s_lo, s_hi;       // start (int64)
     int e_lo, e_hi;       // end (int64)
     uint32_t name;        // noff | nlen << 16   (smem offsets)
-    uint32_t read;        // roff | length up to the first '/' << 16
-    uint32_t rfull;       // full length of the read token
+    uint32_t read;        // roff | rcmp << 16: rcmp = number of read-name bytes the policy compares
     uint32_t flags;       // nf (bits 0-2) | numbad (bit 3) | toolong (bit 4)
+    uint32_t rw[RW];      // first min(rcmp, 32) read-name bytes, zero padded
+};
+
+// scratch shared by one CTA
+struct Smem {
+    uint8_t *s;           // staged bytes
+    uint32_t *sp;         // special bitmap
+    uint16_t *seg;        // per-warp newline segments
+    uint16_t *lines;      // compacted line starts
+    uint32_t (*lowmask)[RW];   // lowmask[e][j]: bytes of word j that belong to the low e bytes of a window
+    Rec *carry;
+    int *wcount;
+    int *flagp;
 };
 
 __device__ __forceinline__ long long rec_start(const Rec &r)
@@ -61,16 +85,36 @@ __device__ __forceinline__ bool is_ws(uint32_t c) { return c == 32u || (c - 9u) 
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-// exact per-byte "== '\n'" mask: 0x80 in every byte of w that equals 0x0A
-__device__ __forceinline__ uint32_t nl_mask(uint32_t w)
+// ---- exact SWAR byte tests: 0x80 in every byte that satisfies the test ----
+__device__ __forceinline__ uint32_t eq_bytes(uint32_t w, uint32_t c4)
 {
-    uint32_t x = w ^ 0x0A0A0A0Au;
+    uint32_t x = w ^ c4;
     uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
-    return ~(t | x | 0x7F7F7F7Fu);
+    return ~(t | x) & 0x80808080u;
 }
-
-// 0x80-per-byte mask -> 4-bit mask (bit j = byte j)
-__device__ __forceinline__ uint32_t bytes_to_nib(uint32_t z) { return (((z >> 7) * 0x00204081u) >> 21) & 15u; }
+__device__ __forceinline__ uint32_t le_bytes_0x20(uint32_t w)
+{
+    uint32_t t = (w & 0x7F7F7F7Fu) + 0x5F5F5F5Fu;     // bit 7 set iff (b & 0x7f) > 0x20
+    return ~(t | w) & 0x80808080u;
+}
+// four 0x80-flag words -> 16-bit mask, bit k = byte k of the 16-byte chunk
+__device__ __forceinline__ uint32_t pack16(uint32_t z0, uint32_t z1, uint32_t z2, uint32_t z3)
+{
+    uint32_t lo = __dp4a(z0, 0x08040201u, 0u);
+    lo = __dp4a(z1, 0x80402010u, lo);                 // 128 * (nib0 | nib1 << 4)
+    uint32_t hi = __dp4a(z2, 0x08040201u, 0u);
+    hi = __dp4a(z3, 0x80402010u, hi);
+    return (lo >> 7) | (hi << 1);
+}
+__device__ __forceinline__ uint32_t nl16_of(const uint4 &v)
+{
+    return pack16(eq_bytes(v.x, 0x0A0A0A0Au), eq_bytes(v.y, 0x0A0A0A0Au), eq_bytes(v.z, 0x0A0A0A0Au), eq_bytes(v.w, 0x0A0A0A0Au));
+}
+__device__ __forceinline__ uint32_t sp16_of(const uint4 &v)
+{
+    return pack16(le_bytes_0x20(v.x) | eq_bytes(v.x, 0x2F2F2F2Fu), le_bytes_0x20(v.y) | eq_bytes(v.y, 0x2F2F2F2Fu),
+                  le_bytes_0x20(v.z) | eq_bytes(v.z, 0x2F2F2F2Fu), le_bytes_0x20(v.w) | eq_bytes(v.w, 0x2F2F2F2Fu));
+}
 
 __device__ __forceinline__ void report(uint64_t *stats, uint64_t file_off, int code)
 {
@@ -78,22 +122,9 @@ __device__ __forceinline__ void report(uint64_t *stats, uint64_t file_off, int c
 }
 
 // ---- contig name -> id ------------------------------------------------
-__device__ __forceinline__ int lookup_name(const DevTable &t, const uint8_t *s, int noff, int nlen)
+__device__ __forceinline__ int lookup_words(const DevTable &t, const uint8_t *s, uint32_t w0, uint32_t w1, uint32_t w2,
+                                            uint32_t w3, int noff, int nlen)
 {
-    // pack the first 16 name bytes from aligned smem words
-    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(s);
-    int a = noff >> 2;
-    int sh = (noff & 3) * 8;
-    uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2], x3 = s32[a + 3], x4 = s32[a + 4];
-    uint32_t w0 = __funnelshift_r(x0, x1, sh), w1 = __funnelshift_r(x1, x2, sh);
-    uint32_t w2 = __funnelshift_r(x2, x3, sh), w3 = __funnelshift_r(x3, x4, sh);
-    if (nlen < 16) {
-        int nb;
-        nb = nlen;      w0 = nb >= 4 ? w0 : (nb <= 0 ? 0u : (w0 & ((1u << (8 * nb)) - 1u)));
-        nb = nlen - 4;  w1 = nb >= 4 ? w1 : (nb <= 0 ? 0u : (w1 & ((1u << (8 * nb)) - 1u)));
-        nb = nlen - 8;  w2 = nb >= 4 ? w2 : (nb <= 0 ? 0u : (w2 & ((1u << (8 * nb)) - 1u)));
-        nb = nlen - 12; w3 = nb >= 4 ? w3 : (nb <= 0 ? 0u : (w3 & ((1u << (8 * nb)) - 1u)));
-    }
     uint32_t h = salsa_name_hash(w0, w1, w2, w3, (uint32_t)nlen) & t.mask;
     for (;;) {
         const uint4 *sp = reinterpret_cast<const uint4 *>(&t.slots[h]);
@@ -112,15 +143,74 @@ __device__ __forceinline__ int lookup_name(const DevTable &t, const uint8_t *s, 
     }
 }
 
-// ---- one line -> record (first four whitespace-separated fields) -------
-// s: smem bytes; p: smem index of the line's first byte; sent: smem index of
-// the '\n' sentinel that ends the staged bytes; trunc: the sentinel stands for
-// a halo cut, not for the end of the data.  Field rules are str.split()'s
-// (make_links.py:62); numbers are strict [+-]?[0-9]{1,18}.
-__device__ __forceinline__ Rec parse_line(const DevTable &t, const uint8_t *s, int p, int sent, bool trunc)
+// 16 bytes at smem offset `off` (any alignment) -> 4 words, bytes >= n cleared
+__device__ __forceinline__ void window4(const Smem &S, int off, int n, uint32_t &w0, uint32_t &w1, uint32_t &w2, uint32_t &w3)
 {
+    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(S.s);
+    int a = off >> 2, sh = (off & 3) * 8;
+    uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2], x3 = s32[a + 3], x4 = s32[a + 4];
+    const uint32_t *mk = S.lowmask[n > 16 ? 16 : n];
+    w0 = __funnelshift_r(x0, x1, sh) & mk[0];
+    w1 = __funnelshift_r(x1, x2, sh) & mk[1];
+    w2 = __funnelshift_r(x2, x3, sh) & mk[2];
+    w3 = __funnelshift_r(x3, x4, sh) & mk[3];
+}
+
+__device__ __forceinline__ int lookup_name(const DevTable &t, const Smem &S, int noff, int nlen)
+{
+    uint32_t w0, w1, w2, w3;
+    window4(S, noff, nlen, w0, w1, w2, w3);
+    return lookup_words(t, S.s, w0, w1, w2, w3, noff, nlen);
+}
+
+// read-name bytes [roff, roff + min(n, 32)) -> rw[], zero padded
+__device__ __forceinline__ void pack_read(const Smem &S, int roff, int n, uint32_t *rw)
+{
+    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(S.s);
+    int a = roff >> 2, sh = (roff & 3) * 8;
+    const uint32_t *mk = S.lowmask[n > 32 ? 32 : n];
+    uint32_t x = s32[a];
+#pragma unroll
+    for (int j = 0; j < RW; j++) {
+        uint32_t y = s32[a + j + 1];
+        rw[j] = __funnelshift_r(x, y, sh) & mk[j];
+        x = y;
+    }
+}
+
+// the n (1..12) decimal digits that END just before smem offset b -> value; false if a byte is not a digit
+__device__ __forceinline__ bool digits12(const Smem &S, int b, int n, long long &val)
+{
+    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(S.s);
+    int q = b - 12;
+    int a = q >> 2, sh = (q & 3) * 8;
+    uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2], x3 = s32[a + 3];
+    const uint32_t *mk = S.lowmask[12 - n];           // the low 12 - n bytes of the window precede the field
+    uint32_t u0 = (__funnelshift_r(x0, x1, sh) ^ 0x30303030u) & ~mk[0];
+    uint32_t u1 = (__funnelshift_r(x1, x2, sh) ^ 0x30303030u) & ~mk[1];
+    uint32_t u2 = (__funnelshift_r(x2, x3, sh) ^ 0x30303030u) & ~mk[2];
+    // byte ^ 0x30 <= 9 exactly for '0'..'9'
+    uint32_t bad = ((((u0 & 0x7F7F7F7Fu) + 0x76767676u) | u0) | (((u1 & 0x7F7F7F7Fu) + 0x76767676u) | u1) |
+                    (((u2 & 0x7F7F7F7Fu) + 0x76767676u) | u2)) & 0x80808080u;
+    uint32_t v0 = __dp4a(u0, 0x0000010Au, 0u) * 100u + __dp4a(u0, 0x010A0000u, 0u);
+    uint32_t v1 = __dp4a(u1, 0x0000010Au, 0u) * 100u + __dp4a(u1, 0x010A0000u, 0u);
+    uint32_t v2 = __dp4a(u2, 0x0000010Au, 0u) * 100u + __dp4a(u2, 0x010A0000u, 0u);
+    val = (long long)((unsigned long long)(v0 * 10000u + v1) * 10000ull + v2);
+    return bad == 0;
+}
+
+// ---- one line -> record, byte-loop parser: str.split() in full (make_links.py:62) ----
+// p: smem index of the line's first byte; sent: smem index of the '\n' sentinel that ends
+// the staged bytes; trunc: the sentinel stands for a halo cut, not for the end of the
+// data.  Numbers are strict [+-]?[0-9]{1,18}.  *rfull = length of the whole read token.
+static __device__ __noinline__ Rec parse_line(const DevTable &t, const Smem &S, int p, int sent, bool trunc, int *rslash, int *rfull)
+{
+    const uint8_t *s = S.s;
     Rec r;
-    r.id = -1; r.s_lo = r.s_hi = r.e_lo = r.e_hi = 0; r.name = 0; r.read = 0; r.rfull = 0; r.flags = 0;
+    r.id = -1; r.s_lo = r.s_hi = r.e_lo = r.e_hi = 0; r.name = 0; r.read = 0; r.flags = 0;
+#pragma unroll
+    for (int j = 0; j < RW; j++) r.rw[j] = 0;
+    *rslash = 0; *rfull = 0;
     uint32_t c = s[p];
     while (c != '\n' && is_ws(c)) c = s[++p];
     int nf = 0;
@@ -130,7 +220,7 @@ __device__ __forceinline__ Rec parse_line(const DevTable &t, const uint8_t *s, i
         do { c = s[++p]; } while (!is_ws(c));
         int nlen = p - noff;
         r.name = (uint32_t)noff | ((uint32_t)nlen << 16);
-        r.id = lookup_name(t, s, noff, nlen);
+        r.id = lookup_name(t, S, noff, nlen);
         nf = 1;
         long long val[2] = {0, 0};
 #pragma unroll
@@ -161,9 +251,10 @@ __device__ __forceinline__ Rec parse_line(const DevTable &t, const uint8_t *s, i
                 nf = 4;
                 int roff = p;
                 while (c != '/' && !is_ws(c)) c = s[++p];      // read.split('/')[0]
-                r.read = (uint32_t)roff | ((uint32_t)(p - roff) << 16);
+                *rslash = p - roff;
                 while (!is_ws(c)) c = s[++p];                  // rest of the token
-                r.rfull = (uint32_t)(p - roff);
+                *rfull = p - roff;
+                r.read = (uint32_t)roff;
             }
         }
     }
@@ -171,12 +262,74 @@ __device__ __forceinline__ Rec parse_line(const DevTable &t, const uint8_t *s, i
     return r;
 }
 
+// ---- one line -> record, branch-free fast path.  Returns false when the line is not
+// provably of the plain form  name SEP digits SEP digits SEP read[/...]  (SEP = one tab
+// or space) with name <= 16, digits <= 12 bytes and all of it inside the staged bytes.
+template <bool NEED_RFULL>
+__device__ __forceinline__ bool parse_fast(const DevTable &t, const Smem &S, int p, int sent, Rec &r, int &rslash, int &rfull)
+{
+    const uint8_t *s = S.s;
+    int i = p >> 5, sh = p & 31;
+    uint32_t a0 = S.sp[i], a1 = S.sp[i + 1], a2 = S.sp[i + 2];
+    unsigned long long M = (unsigned long long)__funnelshift_r(a0, a1, sh) | ((unsigned long long)__funnelshift_r(a1, a2, sh) << 32);
+    if (M & 1ull) return false;                          // leading whitespace / empty line
+    int p1 = __ffsll((long long)M) - 1;
+    M &= M - 1;
+    int p2 = __ffsll((long long)M) - 1;
+    M &= M - 1;
+    int p3 = __ffsll((long long)M) - 1;
+    M &= M - 1;
+    if (!M) return false;                                // fewer than four specials in 64 bytes
+    int p4 = __ffsll((long long)M) - 1;
+    uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
+    bool ok = (c1 == 9u || c1 == 32u) && (c2 == 9u || c2 == 32u) && (c3 == 9u || c3 == 32u) &&
+              (c4 == 47u || c4 == 9u || c4 == 32u || c4 == 10u);
+    int n1 = p2 - p1 - 1, n2 = p3 - p2 - 1, rl = p4 - p3 - 1;
+    ok = ok && p1 <= 16 && n1 >= 1 && n1 <= 12 && n2 >= 1 && n2 <= 12 && rl >= 1 && (p + p4) < sent;
+    rslash = rl;
+    rfull = rl;
+    if (NEED_RFULL) {
+        if (c4 == 47u) {                                 // token continues after the first '/'
+            M &= M - 1;
+            if (!M) return false;
+            int p5 = __ffsll((long long)M) - 1;
+            uint32_t c5 = s[p + p5];
+            ok = ok && (c5 == 9u || c5 == 32u || c5 == 10u) && (p + p5) < sent;
+            rfull = p5 - p3 - 1;
+        }
+    }
+    if (!ok) return false;
+    long long vs, ve;
+    bool d1 = digits12(S, p + p2, n1, vs);
+    bool d2 = digits12(S, p + p3, n2, ve);
+    if (!(d1 && d2)) return false;                       // signs, junk: let the full parser classify it
+    r.name = (uint32_t)p | ((uint32_t)p1 << 16);
+    r.id = lookup_name(t, S, p, p1);
+    r.s_lo = (int)(uint32_t)(unsigned long long)vs; r.s_hi = (int)(uint32_t)((unsigned long long)vs >> 32);
+    r.e_lo = (int)(uint32_t)(unsigned long long)ve; r.e_hi = (int)(uint32_t)((unsigned long long)ve >> 32);
+    r.read = (uint32_t)(p + p3 + 1);
+    r.flags = 4u;
+    return true;
+}
+
 __device__ __forceinline__ bool bytes_equal_back(const uint8_t *s, int a, int b, int n)
 {
-    // compare from the end: consecutive read names differ in their last digits
     for (int i = n - 1; i >= 0; i--)
         if (s[a + i] != s[b + i]) return false;
     return true;
+}
+
+// read-name equality over the policy's compare length (first 32 bytes from the packed words)
+__device__ __forceinline__ bool reads_equal(const uint8_t *s, const Rec &pv, const Rec &cu)
+{
+    uint32_t pl = pv.read >> 16, cl = cu.read >> 16;
+    uint32_t d = pl ^ cl;
+#pragma unroll
+    for (int j = 0; j < RW; j++) d |= pv.rw[j] ^ cu.rw[j];
+    if (d) return false;
+    if (cl <= 32u) return true;
+    int pa = (int)(pv.read & 0xFFFF) + 32, ca = (int)(cu.read & 0xFFFF) + 32;
+    return bytes_equal_back(s, pa, ca, (int)cl - 32);
 }
 
 // contig equality of two adjacent records by NAME (ids when both are known)
@@ -188,29 +341,47 @@ __device__ __forceinline__ bool same_contig(const uint8_t *s, const Rec &pv, con
     return pl == cl && bytes_equal_back(s, pv.name & 0xFFFF, cu.name & 0xFFFF, cl);
 }
 
+__device__ __forceinline__ Rec rec_shfl_up(const Rec &r)
+{
+    Rec o;
+    o.id = __shfl_up_sync(0xffffffffu, r.id, 1);
+    o.s_lo = __shfl_up_sync(0xffffffffu, r.s_lo, 1);
+    o.s_hi = __shfl_up_sync(0xffffffffu, r.s_hi, 1);
+    o.e_lo = __shfl_up_sync(0xffffffffu, r.e_lo, 1);
+    o.e_hi = __shfl_up_sync(0xffffffffu, r.e_hi, 1);
+    o.name = __shfl_up_sync(0xffffffffu, r.name, 1);
+    o.read = __shfl_up_sync(0xffffffffu, r.read, 1);
+    o.flags = __shfl_up_sync(0xffffffffu, r.flags, 1);
+#pragma unroll
+    for (int j = 0; j < RW; j++) o.rw[j] = __shfl_up_sync(0xffffffffu, r.rw[j], 1);
+    return o;
+}
+
 // Process the lines whose first byte lies in (lo, hi] (abase coordinates).
-// sb: abase coordinate of smem byte 0.
-template <class Policy>
-__device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A, uint8_t *s, uint16_t *seg, uint16_t *lines,
-                              Rec *carry, int *wcount, int *flagp, long long sb, long long lo, long long hi, long long l0,
-                              int sent, bool trunc, uint32_t &nlines_acc, uint32_t &npairs_acc)
+// sb: abase coordinate of smem byte 0.  WRITE_SP: also fill the special bitmap
+// of the scanned chunks (the full-tile call; sub-range calls reuse it).
+template <class Policy, bool WRITE_SP>
+__device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A, const Smem &S, long long sb, long long lo,
+                              long long hi, long long l0, int sent, bool trunc, uint32_t &nlines_acc, uint32_t &npairs_acc)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // ---- newline scan: q in [lo, hi) -> line start q + 1 ---------------
-    // valid iff q >= mis and q + 1 < dend
+    uint8_t *s = S.s;
+    // ---- classify + newline scan: q in [lo, hi) -> line start q + 1 (valid iff q >= mis and q + 1 < dend)
     const int nchunks = (int)((hi - lo) >> 4);
     const int cpw = (nchunks + NWARPS - 1) / NWARPS;
     int cnt = 0;                         // this warp's running count (uniform)
     const uint4 *s128 = reinterpret_cast<const uint4 *>(s);
+    uint16_t *sp16 = reinterpret_cast<uint16_t *>(S.sp);
     for (int it = 0; it < cpw; it += 32) {
         int ch = warp * cpw + it + lane;
         bool act = (it + lane) < cpw && ch < nchunks;
         long long q0 = lo + ((long long)ch << 4);
         uint32_t m16 = 0;
         if (act) {
-            uint4 v = s128[(q0 - sb) >> 4];
-            m16 = bytes_to_nib(nl_mask(v.x)) | (bytes_to_nib(nl_mask(v.y)) << 4) | (bytes_to_nib(nl_mask(v.z)) << 8) |
-                  (bytes_to_nib(nl_mask(v.w)) << 12);
+            int ci = (int)((q0 - sb) >> 4);
+            uint4 v = s128[ci];
+            m16 = nl16_of(v);
+            if (WRITE_SP) sp16[ci] = (uint16_t)sp16_of(v);
             // drop newlines outside the data or ending it (q + 1 < dend, q >= mis)
             if (q0 + 16 >= (long long)A.dend || q0 < (long long)A.mis) {
                 long long klo = (long long)A.mis - q0, khi = (long long)A.dend - 1 - q0;
@@ -219,45 +390,52 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
                 m16 &= b > a ? (((1u << b) - 1u) & ~((1u << a) - 1u)) : 0u;
             }
         }
-        int c = __popc(m16);
-        int inc = c;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += o;
-        }
-        int pos = cnt + inc - c;
-        int tot = __shfl_sync(0xffffffffu, inc, 31);
         int sidx = (int)(q0 - sb) + 1;         // smem index of the byte after chunk byte 0
-        while (m16) {
-            int b = __ffs(m16) - 1;
-            m16 &= m16 - 1;
-            if (pos < WCAP) seg[warp * WCAP + pos] = (uint16_t)(sidx + b);
-            pos++;
+        unsigned has = __ballot_sync(0xffffffffu, m16 != 0u);
+        unsigned multi = __ballot_sync(0xffffffffu, (m16 & (m16 - 1u)) != 0u);
+        if (multi == 0u) {                     // at most one newline per 16-byte chunk: rank by ballot
+            int pos = cnt + __popc(has & ((1u << lane) - 1u));
+            if (m16 && pos < WCAP) S.seg[warp * WCAP + pos] = (uint16_t)(sidx + __ffs(m16) - 1);
+            cnt += __popc(has);
+        } else {
+            int c = __popc(m16), inc = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            int pos = cnt + inc - c;
+            int tot = __shfl_sync(0xffffffffu, inc, 31);
+            while (m16) {
+                int b = __ffs(m16) - 1;
+                m16 &= m16 - 1;
+                if (pos < WCAP) S.seg[warp * WCAP + pos] = (uint16_t)(sidx + b);
+                pos++;
+            }
+            cnt += tot;
         }
-        cnt += tot;
     }
     if (lane == 0) {
-        wcount[warp] = cnt;
-        if (cnt > WCAP) atomicOr(flagp, 1);
+        S.wcount[warp] = cnt;
+        if (cnt > WCAP) atomicOr(S.flagp, 1);
     }
     __syncthreads();
-    if (*flagp) return;                  // only from the full-tile call; the caller falls back to subtiles
+    if (*S.flagp) return;                // only from the full-tile call; the caller falls back to subtiles
     int wb = 0, n = 0;
 #pragma unroll
     for (int w = 0; w < NWARPS; w++) {
-        int cw = wcount[w];
+        int cw = S.wcount[w];
         if (w < warp) wb += cw;
         n += cw;
     }
     // lines[0] = the line before the first owned one; lines[1..n] = owned starts
-    for (int i = lane; i < cnt; i += 32) lines[1 + wb + i] = seg[warp * WCAP + i];
+    for (int i = lane; i < cnt; i += 32) S.lines[1 + wb + i] = S.seg[warp * WCAP + i];
     if (n > 0 && warp == 0) {
         // backward search for the start of the previous line: last '\n' before
         // lines[1] - 1, not below max(l0, mis)
         int first = 0;
         for (int w = 0; w < NWARPS; w++)
-            if (wcount[w] > 0) { first = seg[w * WCAP]; break; }
+            if (S.wcount[w] > 0) { first = S.seg[w * WCAP]; break; }
         long long lowpos = l0 > (long long)A.mis ? l0 : (long long)A.mis;
         int low = (int)(lowpos - sb);
         int found = -1;
@@ -268,10 +446,10 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
             if (m) found = base - (__ffs(m) - 1);
         }
         if (lane == 0) {
-            if (found >= 0) lines[0] = (uint16_t)(found + 1);
-            else if (lowpos == (long long)A.mis) lines[0] = (uint16_t)low;     // first line of the buffer
+            if (found >= 0) S.lines[0] = (uint16_t)(found + 1);
+            else if (lowpos == (long long)A.mis) S.lines[0] = (uint16_t)low;     // first line of the buffer
             else {
-                lines[0] = (uint16_t)low;
+                S.lines[0] = (uint16_t)low;
                 report(A.stats, A.base_offset + (uint64_t)(lowpos - A.mis), SALSA_DATA_LINE_TOO_LONG);
             }
         }
@@ -284,49 +462,63 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     for (int r0 = 0; r0 < K; r0 += NTHREADS) {
         int e = r0 + tid;
         Rec rec;
-        rec.id = -1; rec.s_lo = rec.s_hi = rec.e_lo = rec.e_hi = 0; rec.name = rec.read = rec.rfull = 0; rec.flags = 0;
+        rec.id = -1; rec.s_lo = rec.s_hi = rec.e_lo = rec.e_hi = 0; rec.name = rec.read = 0; rec.flags = 0;
+#pragma unroll
+        for (int j = 0; j < RW; j++) rec.rw[j] = 0;
         int lstart = 0;
         if (e < K) {
-            lstart = lines[e];
-            rec = parse_line(A.t, s, lstart, sent, trunc);
+            lstart = S.lines[e];
+            int rslash = 0, rfull = 0;
+            if (!parse_fast<Policy::NEED_RFULL>(A.t, S, lstart, sent, rec, rslash, rfull))
+                rec = parse_line(A.t, S, lstart, sent, trunc, &rslash, &rfull);
+            if ((rec.flags & 7u) == 4u) {
+                int rcmp = Policy::read_cmp_len(rslash, rfull);
+                int roff = (int)(rec.read & 0xFFFF);
+                rec.read = (uint32_t)roff | ((uint32_t)rcmp << 16);
+                pack_read(S, roff, rcmp, rec.rw);
+            }
         }
-        if (lane == 31) carry[warp + 1] = rec;
+        if (lane == 31) S.carry[warp + 1] = rec;
         __syncthreads();
-        Rec pv;
-        pv.id = __shfl_up_sync(0xffffffffu, rec.id, 1);
-        pv.s_lo = __shfl_up_sync(0xffffffffu, rec.s_lo, 1);
-        pv.s_hi = __shfl_up_sync(0xffffffffu, rec.s_hi, 1);
-        pv.e_lo = __shfl_up_sync(0xffffffffu, rec.e_lo, 1);
-        pv.e_hi = __shfl_up_sync(0xffffffffu, rec.e_hi, 1);
-        pv.name = __shfl_up_sync(0xffffffffu, rec.name, 1);
-        pv.read = __shfl_up_sync(0xffffffffu, rec.read, 1);
-        pv.rfull = __shfl_up_sync(0xffffffffu, rec.rfull, 1);
-        pv.flags = __shfl_up_sync(0xffffffffu, rec.flags, 1);
+        Rec pv = rec_shfl_up(rec);
         int pstart = __shfl_up_sync(0xffffffffu, lstart, 1);
-        if (lane == 0) { pv = carry[warp]; pstart = -2; }
+        if (lane == 0) { pv = S.carry[warp]; pstart = -2; }
         if (e >= 1 && e < K) {
             nlines_acc++;
             uint64_t off = A.base_offset + (uint64_t)((long long)lstart + sb - (long long)A.mis);
             // is the previous line the very first line of the caller's buffer?
-            bool prev_is_first = (e == 1) ? (lines[0] == first_line_idx && sb <= 0) : (pstart == first_line_idx && sb <= 0);
+            bool prev_is_first = sb <= 0 && ((e == 1) ? (S.lines[0] == first_line_idx) : (pstart == first_line_idx));
             if (Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
         }
         __syncthreads();
-        if (tid == NTHREADS - 1) carry[0] = rec;
+        if (tid == NTHREADS - 1) S.carry[0] = rec;
     }
     __syncthreads();
 }
 
+constexpr size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+constexpr size_t OFF_SP = align16(SMEM_BYTES);
+constexpr size_t OFF_SEG = OFF_SP + align16(SPWORDS * 4);
+constexpr size_t OFF_LINES = OFF_SEG + align16(LCAP * 2);
+constexpr size_t OFF_MASK = OFF_LINES + align16((LCAP + 8) * 2);
+constexpr size_t OFF_CARRY = OFF_MASK + align16(33 * RW * 4);
+constexpr size_t OFF_WCOUNT = OFF_CARRY + align16((NWARPS + 1) * sizeof(Rec));
+constexpr size_t DYN_SMEM = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));
+
 template <class Policy>
-__global__ void __launch_bounds__(NTHREADS, 4) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
+__global__ void __launch_bounds__(NTHREADS, 3) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *s = smem;                                         // SMEM_BYTES
-    uint16_t *seg = reinterpret_cast<uint16_t *>(smem + SMEM_BYTES);        // LCAP
-    uint16_t *lines = seg + LCAP;                              // LCAP + 8
-    Rec *carry = reinterpret_cast<Rec *>(lines + LCAP + 8);    // NWARPS + 1
-    int *wcount = reinterpret_cast<int *>(carry + NWARPS + 1); // NWARPS
-    int *flagp = wcount + NWARPS;
+    Smem S;
+    S.s = smem;
+    S.sp = reinterpret_cast<uint32_t *>(smem + OFF_SP);
+    S.seg = reinterpret_cast<uint16_t *>(smem + OFF_SEG);
+    S.lines = reinterpret_cast<uint16_t *>(smem + OFF_LINES);
+    S.lowmask = reinterpret_cast<uint32_t (*)[RW]>(smem + OFF_MASK);
+    S.carry = reinterpret_cast<Rec *>(smem + OFF_CARRY);
+    S.wcount = reinterpret_cast<int *>(smem + OFF_WCOUNT);
+    S.flagp = S.wcount + NWARPS;
+    uint8_t *s = S.s;
     __shared__ __align__(8) uint64_t bar;
 
     const int tid = threadIdx.x;
@@ -340,7 +532,7 @@ __global__ void __launch_bounds__(NTHREADS, 4) bed_scan_kernel(typename Policy::
     const bool trunc = l1 < (long long)A.dend;
 
     if (tid == 0) {
-        *flagp = 0;
+        *S.flagp = 0;
         uint32_t b = smem_u32(&bar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -354,8 +546,14 @@ __global__ void __launch_bounds__(NTHREADS, 4) bed_scan_kernel(typename Policy::
                      "l"(A.abase + l0), "r"(nb), "r"(b)
                      : "memory");
     }
-    // sentinel + pad (generic-proxy writes to bytes the bulk copy does not touch)
+    // while the copy is in flight: sentinel bytes, byte-mask table, bitmap guard words
     if (tid < 32) s[sent + tid] = '\n';
+    for (int i = tid; i < 33 * RW; i += NTHREADS) {
+        int e = i / RW, j = i % RW;
+        int nbv = e - 4 * j;
+        S.lowmask[e][j] = nbv >= 4 ? 0xFFFFFFFFu : (nbv <= 0 ? 0u : ((1u << (8 * nbv)) - 1u));
+    }
+    for (int i = tid; i < SPWORDS; i += NTHREADS) S.sp[i] = 0xFFFFFFFFu;     // everything "special" until classified
     {
         uint32_t b = smem_u32(&bar);
         uint32_t done = 0;
@@ -379,20 +577,31 @@ __global__ void __launch_bounds__(NTHREADS, 4) bed_scan_kernel(typename Policy::
     }
     __syncthreads();
 
+    const long long hi = t1 < dend16 ? t1 : dend16;
+    // special bitmap of the two halos (the owned range is classified inside process_range)
+    {
+        const uint4 *s128 = reinterpret_cast<const uint4 *>(s);
+        uint16_t *sp16 = reinterpret_cast<uint16_t *>(S.sp);
+        const int nback = (int)((t0 - l0) >> 4), nfwd = (int)((l1 - hi) >> 4);
+        for (int i = tid; i < nback + nfwd; i += NTHREADS) {
+            long long q0 = i < nback ? l0 + ((long long)i << 4) : hi + ((long long)(i - nback) << 4);
+            int ci = (int)((q0 - sb) >> 4);
+            sp16[ci] = (uint16_t)sp16_of(s128[ci]);
+        }
+    }
     uint32_t nlines = 0, npairs = 0;
-    long long hi = t1 < dend16 ? t1 : dend16;
-    process_range<Policy>(PA, A, s, seg, lines, carry, wcount, flagp, sb, t0, hi, l0, sent, trunc, nlines, npairs);
-    if (*flagp) {
+    process_range<Policy, true>(PA, A, S, sb, t0, hi, l0, sent, trunc, nlines, npairs);
+    if (*S.flagp) {
         // > WCAP line starts inside one warp's 4 KB: redo the tile in 2 KB ranges,
         // which cannot overflow (a line start needs at least one byte)
         __syncthreads();
         nlines = npairs = 0;
         for (long long lo = t0; lo < hi; lo += SUBTILE) {
             __syncthreads();
-            if (tid == 0) *flagp = 0;
+            if (tid == 0) *S.flagp = 0;
             __syncthreads();
             long long h2 = lo + SUBTILE < hi ? lo + SUBTILE : hi;
-            process_range<Policy>(PA, A, s, seg, lines, carry, wcount, flagp, sb, lo, h2, l0, sent, trunc, nlines, npairs);
+            process_range<Policy, false>(PA, A, S, sb, lo, h2, l0, sent, trunc, nlines, npairs);
         }
     }
     // ---- statistics: one atomic pair per CTA -----------------------------
@@ -414,8 +623,6 @@ __global__ void __launch_bounds__(NTHREADS, 4) bed_scan_kernel(typename Policy::
         if (red[1]) atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)red[1]);
     }
 }
-
-constexpr size_t DYN_SMEM = SMEM_BYTES + LCAP * 2 + (LCAP + 8) * 2 + (NWARPS + 1) * sizeof(Rec) + (NWARPS + 1) * sizeof(int);
 
 template <class Policy>
 int launch_scan(const typename Policy::Args &PA, const DevTable &t, const void *d_bed, size_t nbytes, uint64_t base_offset,

@@ -47,6 +47,9 @@ struct CovArgs {
 template <bool JOINS>
 struct CovPolicy {
     typedef CovArgs Args;
+    static constexpr bool NEED_RFULL = true;
+    // read.substr(0, len-2) == prev_read.substr(0, len-2)   (size_t wrap for len < 2: the whole string)
+    static __device__ __forceinline__ int read_cmp_len(int /*rslash*/, int rfull) { return rfull >= 2 ? rfull - 2 : rfull; }
     static __device__ __forceinline__ bool pair(const CovArgs &C, const ScanArgs &A, const uint8_t *s, const Rec &pv,
                                                 const Rec &cu, uint64_t line_off, bool prev_is_first)
     {
@@ -61,11 +64,7 @@ struct CovPolicy {
         if (C.first_chunk && prev_is_first) return false;          // the first line is never parsed: prev_* are still initial
         if ((pv.flags & 7u) < 4u || (pv.flags & 8u)) return false; // after a malformed line nothing counts (rerun truncates)
         if (pv.id != cu.id) return false;                          // prev_contig == contig
-        // read.substr(0, len-2) == prev_read.substr(0, len-2)   (size_t wrap for len < 2: whole string)
-        int pl = (int)pv.rfull, cl = (int)cu.rfull;
-        pl = pl >= 2 ? pl - 2 : pl;
-        cl = cl >= 2 ? cl - 2 : cl;
-        if (pl != cl || !bytes_equal_back(s, pv.read & 0xFFFF, cu.read & 0xFFFF, cl)) return false;
+        if (!reads_equal(s, pv, cu)) return false;                // over read_cmp_len() bytes
         const long long ps = rec_start(pv), pe = rec_end(pv), cs = rec_start(cu), ce = rec_end(cu);
         const long long len = C.len[cu.id];
         const long long cutoff = (long long)(int)(len / 10);       // unordered_map<string,int> contig2cutoff
