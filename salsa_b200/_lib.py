@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libsalsa_b200.so')
+LIB_PATH = os.environ.get('SALSA_B200_LIB') or os.path.join(_HERE, 'libsalsa_b200.so')   # override: A/B builds
 _lib = None
 
 c_void_p, c_size_t, c_u64, c_i32, c_i64 = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int32, C.c_int64

@@ -30,7 +30,13 @@
 
 namespace bedscan {
 
-constexpr int TILE = 32768;
+#ifndef SALSA_TILE
+#define SALSA_TILE 32768
+#endif
+#ifndef SALSA_MINBLOCKS
+#define SALSA_MINBLOCKS 3
+#endif
+constexpr int TILE = SALSA_TILE;
 constexpr int HALO = SALSA_MAX_LINE;   // 1024
 constexpr int NTHREADS = 256;
 constexpr int NWARPS = NTHREADS / 32;
@@ -299,12 +305,20 @@ __device__ __forceinline__ bool parse_fast(const DevTable &t, const Smem &S, int
         }
     }
     if (!ok) return false;
+    // issue the first name-table probe now; its latency hides behind the digit conversion
+    uint32_t w0, w1, w2, w3;
+    window4(S, p, p1, w0, w1, w2, w3);
+    uint32_t h = salsa_name_hash(w0, w1, w2, w3, (uint32_t)p1) & t.mask;
+    const uint4 *slot = reinterpret_cast<const uint4 *>(&t.slots[h]);
+    uint4 k0 = __ldg(slot), m0 = __ldg(slot + 1);
     long long vs, ve;
     bool d1 = digits12(S, p + p2, n1, vs);
     bool d2 = digits12(S, p + p3, n2, ve);
     if (!(d1 && d2)) return false;                       // signs, junk: let the full parser classify it
     r.name = (uint32_t)p | ((uint32_t)p1 << 16);
-    r.id = lookup_name(t, S, p, p1);
+    if (m0.x == (uint32_t)p1 && k0.x == w0 && k0.y == w1 && k0.z == w2 && k0.w == w3) r.id = (int)m0.y;   // p1 <= 16: exact
+    else if (m0.x == 0xFFFFFFFFu) r.id = -1;
+    else r.id = lookup_words(t, s, w0, w1, w2, w3, p, p1);                                                // collision: probe on
     r.s_lo = (int)(uint32_t)(unsigned long long)vs; r.s_hi = (int)(uint32_t)((unsigned long long)vs >> 32);
     r.e_lo = (int)(uint32_t)(unsigned long long)ve; r.e_hi = (int)(uint32_t)((unsigned long long)ve >> 32);
     r.read = (uint32_t)(p + p3 + 1);
@@ -372,25 +386,30 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     int cnt = 0;                         // this warp's running count (uniform)
     const uint4 *s128 = reinterpret_cast<const uint4 *>(s);
     uint16_t *sp16 = reinterpret_cast<uint16_t *>(S.sp);
+    // everything below in smem indices (int): a newline at index x counts iff vlo <= x < vhi
+    const int c0 = (int)((lo - sb) >> 4);                    // first chunk of the range
+    const long long vlo_ll = (long long)A.mis - sb, vhi_ll = (long long)A.dend - 1 - sb;
+    const int vlo = vlo_ll < 0 ? 0 : (int)vlo_ll;
+    const int vhi = vhi_ll > (long long)SMEM_BYTES ? SMEM_BYTES : (int)vhi_ll;
     for (int it = 0; it < cpw; it += 32) {
         int ch = warp * cpw + it + lane;
         bool act = (it + lane) < cpw && ch < nchunks;
-        long long q0 = lo + ((long long)ch << 4);
+        int ci = c0 + ch;
+        int x0 = ci << 4;                                    // smem index of chunk byte 0
         uint32_t m16 = 0;
         if (act) {
-            int ci = (int)((q0 - sb) >> 4);
             uint4 v = s128[ci];
             m16 = nl16_of(v);
             if (WRITE_SP) sp16[ci] = (uint16_t)sp16_of(v);
             // drop newlines outside the data or ending it (q + 1 < dend, q >= mis)
-            if (q0 + 16 >= (long long)A.dend || q0 < (long long)A.mis) {
-                long long klo = (long long)A.mis - q0, khi = (long long)A.dend - 1 - q0;
-                int a = klo < 0 ? 0 : (klo > 16 ? 16 : (int)klo);
-                int b = khi < 0 ? 0 : (khi > 16 ? 16 : (int)khi);
+            if (x0 < vlo || x0 + 16 > vhi) {
+                int a = vlo - x0, b = vhi - x0;
+                a = a < 0 ? 0 : (a > 16 ? 16 : a);
+                b = b < 0 ? 0 : (b > 16 ? 16 : b);
                 m16 &= b > a ? (((1u << b) - 1u) & ~((1u << a) - 1u)) : 0u;
             }
         }
-        int sidx = (int)(q0 - sb) + 1;         // smem index of the byte after chunk byte 0
+        int sidx = x0 + 1;                     // smem index of the byte after chunk byte 0
         unsigned has = __ballot_sync(0xffffffffu, m16 != 0u);
         unsigned multi = __ballot_sync(0xffffffffu, (m16 & (m16 - 1u)) != 0u);
         if (multi == 0u) {                     // at most one newline per 16-byte chunk: rank by ballot
@@ -506,7 +525,7 @@ constexpr size_t OFF_WCOUNT = OFF_CARRY + align16((NWARPS + 1) * sizeof(Rec));
 constexpr size_t DYN_SMEM = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));
 
 template <class Policy>
-__global__ void __launch_bounds__(NTHREADS, 3) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
+__global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     Smem S;
@@ -549,12 +568,17 @@ __global__ void __launch_bounds__(NTHREADS, 3) bed_scan_kernel(typename Policy::
     // while the copy is in flight: sentinel bytes, byte-mask table, bitmap guard words
     if (tid < 32) s[sent + tid] = '\n';
     for (int i = tid; i < 33 * RW; i += NTHREADS) {
-        int e = i / RW, j = i % RW;
+        int e = i >> 3, j = i & 7;
         int nbv = e - 4 * j;
         S.lowmask[e][j] = nbv >= 4 ? 0xFFFFFFFFu : (nbv <= 0 ? 0u : ((1u << (8 * nbv)) - 1u));
     }
-    for (int i = tid; i < SPWORDS; i += NTHREADS) S.sp[i] = 0xFFFFFFFFu;     // everything "special" until classified
+    // bitmap words at and beyond the end of the staged bytes read as "special" (the chunk
+    // classification below overwrites the halves it owns)
     {
+        int w0 = (sent >> 5) - 1 + tid;
+        if (tid < 8 && w0 >= 0 && w0 < SPWORDS) S.sp[w0] = 0xFFFFFFFFu;
+    }
+    if (tid < 32) {                      // one warp waits for the bulk copy; the rest meet it at the barrier below
         uint32_t b = smem_u32(&bar);
         uint32_t done = 0;
         while (!done) {
