@@ -52,6 +52,9 @@ extern "C" {
                                       that precedes a tile boundary, exceed
                                       SALSA_MAX_LINE bytes (library limit)       */
 
+#define SALSA_DATA_AVOID_CHAIN 9   /* avoid mode: more than 64 consecutive lines on avoid-listed
+                                      contigs directly before a tile boundary (library limit)     */
+
 #define SALSA_MAX_LINE 1024        /* bytes; see SALSA_DATA_LINE_TOO_LONG */
 
 typedef struct salsa_ctx salsa_ctx;
@@ -116,8 +119,10 @@ int salsa_ingest_stats_read(const uint64_t *d_stats, salsa_ingest_stats *h_out, 
  *       (make_links.py:66-68).  To ingest a file in chunks (or shards on
  *       several GPUs) start each chunk at the first byte of the previous
  *       chunk's LAST line: chunks overlap by exactly one line.  With a
- *       non-empty avoid set a chunk must additionally start on a line whose
- *       contig is in no avoid pair (salsa_bed_split finds such boundaries).
+ *       non-empty avoid set (salsa_avoid_set) the scan reproduces the
+ *       reference's stale prev_line rule (make_links.py:72-74: an avoided
+ *       pair `continue`s WITHOUT advancing prev_line), and a chunk must
+ *       additionally start on a line whose contig is in no avoid pair.
  *   d_table : uint64 [n*n*4], n = salsa_names_count(); cell
  *       ((first*n + second)*4 + ends) with first < second, ends bit1 = first
  *       is 'E', bit0 = second is 'E'.  Counts are ADDED (zero it first).

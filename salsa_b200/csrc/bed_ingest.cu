@@ -18,9 +18,10 @@ struct LinkArgs {
     uint64_t cap_mask;        // sparse only
 };
 
-template <bool SPARSE>
+template <bool SPARSE, bool AVOID_>
 struct LinkPolicy {
     typedef LinkArgs Args;
+    static constexpr bool AVOID = AVOID_;   // links_avoid_iteration_N present (make_links.py:29-35,72-74)
     static constexpr bool NEED_RFULL = false;
     // make_links.py:78 compares read.split('/')[0]
     static __device__ __forceinline__ int read_cmp_len(int rslash, int /*rfull*/) { return rslash; }
@@ -119,8 +120,6 @@ static int check_ingest_args(salsa_ctx *ctx, const void *d_bed, size_t nbytes, c
 {
     if (!ctx || (!d_bed && nbytes) || !table || !stats) SALSA_FAIL(SALSA_ERR_ARG, "salsa_bed_ingest: NULL argument");
     if (ctx->n <= 0) SALSA_FAIL(SALSA_ERR_ARG, "salsa_bed_ingest: call salsa_names_build first");
-    if (ctx->t.navoid > 0)
-        SALSA_FAIL(SALSA_ERR_UNSUPPORTED, "salsa_bed_ingest: avoid set present; use salsa_bed_ingest_avoid");
     CUDA_TRY(cudaSetDevice(ctx->device));
     return SALSA_OK;
 }
@@ -131,7 +130,9 @@ extern "C" int salsa_bed_ingest_dense(salsa_ctx *ctx, const void *d_bed, size_t 
     int rc = check_ingest_args(ctx, d_bed, nbytes, d_table, d_stats);
     if (rc) return rc;
     LinkArgs L{d_table, NULL, 0};
-    return bedscan::launch_scan<LinkPolicy<false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
+    if (ctx->t.navoid > 0)
+        return bedscan::launch_scan<LinkPolicy<false, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
+    return bedscan::launch_scan<LinkPolicy<false, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
 }
 
 extern "C" int salsa_sparse_reset(uint64_t *d_keys, uint64_t *d_counts, size_t capacity, void *stream)
@@ -152,7 +153,9 @@ extern "C" int salsa_bed_ingest_sparse(salsa_ctx *ctx, const void *d_bed, size_t
     if (!d_keys || capacity == 0 || (capacity & (capacity - 1)))
         SALSA_FAIL(SALSA_ERR_ARG, "salsa_bed_ingest_sparse: capacity must be a power of two");
     LinkArgs L{d_counts, d_keys, capacity - 1};
-    return bedscan::launch_scan<LinkPolicy<true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
+    if (ctx->t.navoid > 0)
+        return bedscan::launch_scan<LinkPolicy<true, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
+    return bedscan::launch_scan<LinkPolicy<true, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
 }
 
 // Host-resident BED: chunked H2D copies overlapped with the kernel.  Chunks
@@ -165,6 +168,9 @@ extern "C" int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, si
     if (!h_bed && nbytes) SALSA_FAIL(SALSA_ERR_ARG, "h_bed is NULL");
     if (chunk_bytes < 4 * (size_t)SALSA_MAX_LINE || (chunk_bytes & 15))
         SALSA_FAIL(SALSA_ERR_ARG, "chunk_bytes must be a multiple of 16 and >= %d", 4 * SALSA_MAX_LINE);
+    if (ctx->t.navoid > 0)
+        SALSA_FAIL(SALSA_ERR_UNSUPPORTED, "salsa_bed_ingest_dense_host: with an avoid set, chunk on the host at lines whose "
+                                          "contig is in no avoid pair and call salsa_bed_ingest_dense per chunk");
     rc = salsa_ctx_streams(ctx);
     if (rc) return rc;
     const char *h = (const char *)h_bed;
@@ -190,7 +196,7 @@ extern "C" int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, si
         CUDA_TRY(cudaMemcpyAsync(dst, h + pos, end - pos, cudaMemcpyHostToDevice, ctx->s_copy));
         CUDA_TRY(cudaEventRecord(ctx->ev_copy[k & 1], ctx->s_copy));
         CUDA_TRY(cudaStreamWaitEvent(ctx->s_comp, ctx->ev_copy[k & 1], 0));
-        rc = bedscan::launch_scan<LinkPolicy<false>>(L, ctx->t, dst, end - pos, pos, d_stats, ctx->s_comp);
+        rc = bedscan::launch_scan<LinkPolicy<false, false>>(L, ctx->t, dst, end - pos, pos, d_stats, ctx->s_comp);
         if (rc) return rc;
         CUDA_TRY(cudaEventRecord(ctx->ev_comp[k & 1], ctx->s_comp));
         pos = next;

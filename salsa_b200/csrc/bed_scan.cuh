@@ -43,7 +43,8 @@ constexpr int NWARPS = NTHREADS / 32;
 constexpr int LCAP = 2048;             // line starts per scan range
 constexpr int WCAP = LCAP / NWARPS;    // per-warp segment
 constexpr int SUBTILE = 2048;          // fallback range: <= 2048 line starts by construction
-constexpr int SMEM_BYTES = HALO + TILE + HALO + 32;
+constexpr int SPARE_OFF = HALO + TILE + HALO + 32;      // one spare line (avoid mode: a line fetched from before the tile)
+constexpr int SMEM_BYTES = SPARE_OFF + HALO + 64;
 constexpr int SPWORDS = SMEM_BYTES / 32 + 4;   // special-byte bitmap, 1 bit per staged byte (+ guard words)
 constexpr int RW = 8;                  // read-name words carried per record (32 bytes)
 
@@ -76,7 +77,15 @@ struct Smem {
     Rec *carry;
     int *wcount;
     int *flagp;
+    // avoid mode only (Policy::AVOID)
+    int *idv;             // per line entry: contig id | IDV_INVOLVED, -1 unknown
+    Rec *ext;             // record of the effective previous line when it lies before the tile
+    int *extinfo;         // [0] entry 0 was skipped, [1] contig id of *ext
 };
+
+constexpr int IDV_INVOLVED = 0x40000000;
+__device__ __forceinline__ int idv_id(int v) { return v < 0 ? -1 : (v & 0x3FFFFFFF); }
+__device__ __forceinline__ bool idv_inv(int v) { return v >= 0 && (v & IDV_INVOLVED); }
 
 __device__ __forceinline__ long long rec_start(const Rec &r)
 {
@@ -371,6 +380,99 @@ __device__ __forceinline__ Rec rec_shfl_up(const Rec &r)
     return o;
 }
 
+// one line -> record: fast path, else the full parser; read name packed per policy
+template <class Policy>
+__device__ __forceinline__ Rec parse_any(const ScanArgs &A, const Smem &S, int lstart, int sent, bool trunc, bool allow_fast)
+{
+    Rec rec;
+    rec.id = -1; rec.s_lo = rec.s_hi = rec.e_lo = rec.e_hi = 0; rec.name = rec.read = 0; rec.flags = 0;
+#pragma unroll
+    for (int j = 0; j < RW; j++) rec.rw[j] = 0;
+    int rslash = 0, rfull = 0;
+    if (!allow_fast || !parse_fast<Policy::NEED_RFULL>(A.t, S, lstart, sent, rec, rslash, rfull))
+        rec = parse_line(A.t, S, lstart, sent, trunc, &rslash, &rfull);
+    if ((rec.flags & 7u) == 4u) {
+        int rcmp = Policy::read_cmp_len(rslash, rfull);
+        int roff = (int)(rec.read & 0xFFFF);
+        rec.read = (uint32_t)roff | ((uint32_t)rcmp << 16);
+        pack_read(S, roff, rcmp, rec.rw);
+    }
+    return rec;
+}
+
+// ---- avoid list (links_avoid_iteration_N, make_links.py:29-35,72-74) ------
+// `continue` on an avoided contig pair leaves prev_line untouched, so the line a
+// pair is formed with is the last NON-SKIPPED line.  A line whose contig is in no
+// avoid pair can never be skipped: chains of dependent decisions only run through
+// consecutive "involved" lines and are resolved by walking back to the nearest
+// line that is certainly kept and replaying forward.
+__device__ __forceinline__ bool avoid_has(const DevTable &t, int a, int b)
+{
+    if (a < 0 || b < 0 || a == b) return false;
+    unsigned long long key = ((unsigned long long)(uint32_t)a << 32) | (uint32_t)b;
+    int lo = 0, hi = t.navoid;
+    while (lo < hi) {
+        int mid = (lo + hi) >> 1;
+        if (t.avoid[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo < t.navoid && t.avoid[lo] == key;
+}
+
+// copy the line that starts at abase coordinate st (length len) into the spare buffer and parse it
+template <class Policy>
+__device__ Rec parse_global_line(const ScanArgs &A, const Smem &S, long long st, int len)
+{
+    for (int i = 0; i < len; i++) S.s[SPARE_OFF + i] = A.abase[st + i];
+    S.s[SPARE_OFF + len] = '\n';
+    return parse_any<Policy>(A, S, SPARE_OFF, SPARE_OFF + len, false, false);
+}
+
+// Thread 0: was entry 0 (the line before the first owned line) skipped, and if so which
+// earlier line is the effective "previous" of the first owned line?
+template <class Policy>
+__device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
+{
+    S.extinfo[0] = 0;
+    S.extinfo[1] = -1;
+    const int v0 = S.idv[0];
+    const long long g0 = sb + (long long)S.lines[0];
+    const long long mis = (long long)A.mis;
+    if (!idv_inv(v0) || g0 <= mis) return;            // certainly kept (or the buffer's first line: always "previous")
+    constexpr int MAXC = 64;
+    long long cst[MAXC];
+    int clen[MAXC], cid[MAXC];
+    int nc = 0;
+    long long cur = g0;
+    bool anchored = false;
+    while (nc < MAXC) {
+        long long e = cur - 1;                        // the '\n' that ends the previous line
+        long long st = e;
+        while (st > mis && A.abase[st - 1] != '\n' && e - st <= SALSA_MAX_LINE) st--;
+        if (e - st > SALSA_MAX_LINE) {
+            report(A.stats, A.base_offset + (uint64_t)(st - mis), SALSA_DATA_LINE_TOO_LONG);
+            return;
+        }
+        Rec r = parse_global_line<Policy>(A, S, st, (int)(e - st));
+        cst[nc] = st; clen[nc] = (int)(e - st); cid[nc] = r.id;
+        nc++;
+        bool inv = r.id >= 0 && (A.t.meta[r.id].flags & CTG_INVOLVED);
+        if (!inv || st <= mis) { anchored = true; break; }
+        cur = st;
+    }
+    if (!anchored) {                                  // library limit: > 64 consecutive lines on avoid-listed contigs before a tile
+        report(A.stats, A.base_offset + (uint64_t)(g0 - mis), SALSA_DATA_AVOID_CHAIN);
+        return;
+    }
+    int prev = nc - 1;                                // the anchor; cst[0] is the line right before entry 0
+    for (int k = nc - 2; k >= 0; k--)
+        if (!avoid_has(A.t, cid[prev], cid[k])) prev = k;
+    if (avoid_has(A.t, cid[prev], idv_id(v0))) {
+        *S.ext = parse_global_line<Policy>(A, S, cst[prev], clen[prev]);   // stays in the spare buffer for byte compares
+        S.extinfo[0] = 1;
+        S.extinfo[1] = cid[prev];
+    }
+}
+
 // Process the lines whose first byte lies in (lo, hi] (abase coordinates).
 // sb: abase coordinate of smem byte 0.  WRITE_SP: also fill the special bitmap
 // of the scanned chunks (the full-tile call; sub-range calls reuse it).
@@ -478,6 +580,18 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     // ---- parse + pair ---------------------------------------------------
     const int K = n + 1;
     const int first_line_idx = (int)((long long)A.mis - sb);     // smem index of the buffer's first line (tile 0 only)
+    if (Policy::AVOID) {
+        // pass A: contig id (+ "in some avoid pair") of every line; thread 0 settles what happened before the tile
+        for (int e = tid; e < K; e += NTHREADS) {
+            Rec r = parse_any<Policy>(A, S, S.lines[e], sent, trunc, true);
+            int v = r.id;
+            if (v >= 0 && (A.t.meta[v].flags & CTG_INVOLVED)) v |= IDV_INVOLVED;
+            S.idv[e] = v;
+        }
+        __syncthreads();
+        if (tid == 0) resolve_entry0<Policy>(A, S, sb);
+        __syncthreads();
+    }
     for (int r0 = 0; r0 < K; r0 += NTHREADS) {
         int e = r0 + tid;
         Rec rec;
@@ -487,15 +601,7 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
         int lstart = 0;
         if (e < K) {
             lstart = S.lines[e];
-            int rslash = 0, rfull = 0;
-            if (!parse_fast<Policy::NEED_RFULL>(A.t, S, lstart, sent, rec, rslash, rfull))
-                rec = parse_line(A.t, S, lstart, sent, trunc, &rslash, &rfull);
-            if ((rec.flags & 7u) == 4u) {
-                int rcmp = Policy::read_cmp_len(rslash, rfull);
-                int roff = (int)(rec.read & 0xFFFF);
-                rec.read = (uint32_t)roff | ((uint32_t)rcmp << 16);
-                pack_read(S, roff, rcmp, rec.rw);
-            }
+            rec = parse_any<Policy>(A, S, lstart, sent, trunc, true);
         }
         if (lane == 31) S.carry[warp + 1] = rec;
         __syncthreads();
@@ -505,9 +611,29 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
         if (e >= 1 && e < K) {
             nlines_acc++;
             uint64_t off = A.base_offset + (uint64_t)((long long)lstart + sb - (long long)A.mis);
+            bool skipped = false;
+            if (Policy::AVOID) {
+                // the line this one is paired with is the last non-skipped line (make_links.py:72-74)
+                if (idv_inv(S.idv[e - 1])) {
+                    int j = e - 1;
+                    while (j > 0 && idv_inv(S.idv[j])) j--;
+                    int prev = j, pid = idv_id(S.idv[j]);
+                    if (j == 0 && S.extinfo[0]) { prev = -1; pid = S.extinfo[1]; }
+                    for (int k = j + 1; k <= e; k++) {
+                        int idk = idv_id(S.idv[k]);
+                        bool sk = avoid_has(A.t, pid, idk);
+                        if (k == e) { skipped = sk; break; }
+                        if (!sk) { prev = k; pid = idk; }
+                    }
+                    if (!skipped && prev != e - 1) {
+                        if (prev < 0) pv = *S.ext;
+                        else pv = parse_any<Policy>(A, S, S.lines[prev], sent, trunc, true);
+                    }
+                }
+            }
             // is the previous line the very first line of the caller's buffer?
             bool prev_is_first = sb <= 0 && ((e == 1) ? (S.lines[0] == first_line_idx) : (pstart == first_line_idx));
-            if (Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
+            if (!skipped && Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
         }
         __syncthreads();
         if (tid == NTHREADS - 1) S.carry[0] = rec;
@@ -522,7 +648,13 @@ constexpr size_t OFF_LINES = OFF_SEG + align16(LCAP * 2);
 constexpr size_t OFF_MASK = OFF_LINES + align16((LCAP + 8) * 2);
 constexpr size_t OFF_CARRY = OFF_MASK + align16(33 * RW * 4);
 constexpr size_t OFF_WCOUNT = OFF_CARRY + align16((NWARPS + 1) * sizeof(Rec));
-constexpr size_t DYN_SMEM = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));
+constexpr size_t OFF_IDV = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));       // avoid mode only from here
+constexpr size_t OFF_EXT = OFF_IDV + align16((LCAP + 8) * sizeof(int));
+constexpr size_t OFF_EXTINFO = OFF_EXT + align16(sizeof(Rec));
+constexpr size_t DYN_SMEM_PLAIN = OFF_IDV;
+constexpr size_t DYN_SMEM_AVOID = OFF_EXTINFO + 16;
+template <class Policy>
+constexpr size_t dyn_smem() { return Policy::AVOID ? DYN_SMEM_AVOID : DYN_SMEM_PLAIN; }
 
 template <class Policy>
 __global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
@@ -537,6 +669,9 @@ __global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typ
     S.carry = reinterpret_cast<Rec *>(smem + OFF_CARRY);
     S.wcount = reinterpret_cast<int *>(smem + OFF_WCOUNT);
     S.flagp = S.wcount + NWARPS;
+    S.idv = reinterpret_cast<int *>(smem + OFF_IDV);
+    S.ext = reinterpret_cast<Rec *>(smem + OFF_EXT);
+    S.extinfo = reinterpret_cast<int *>(smem + OFF_EXTINFO);
     uint8_t *s = S.s;
     __shared__ __align__(8) uint64_t bar;
 
@@ -664,8 +799,8 @@ int launch_scan(const typename Policy::Args &PA, const DevTable &t, const void *
     uint64_t ntiles = (A.dend + TILE - 1) / TILE;
     if (ntiles > 0x7fffffffull) SALSA_FAIL(SALSA_ERR_ARG, "BED chunk too large (%zu bytes)", nbytes);
     // per device and cheap, so simply every launch
-    CUDA_TRY(cudaFuncSetAttribute(bed_scan_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DYN_SMEM));
-    bed_scan_kernel<Policy><<<(unsigned)ntiles, NTHREADS, DYN_SMEM, st>>>(PA, A);
+    CUDA_TRY(cudaFuncSetAttribute(bed_scan_kernel<Policy>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem<Policy>()));
+    bed_scan_kernel<Policy><<<(unsigned)ntiles, NTHREADS, dyn_smem<Policy>(), st>>>(PA, A);
     CUDA_TRY(cudaGetLastError());
     return SALSA_OK;
 }

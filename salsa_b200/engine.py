@@ -100,6 +100,7 @@ class Engine:
         pairs = np.array([[idx[a], idx[b]] for a, b in avoid], dtype=np.int32).reshape(-1, 2)
         check(self.L.salsa_avoid_set(self.ctx, pairs.ctypes.data if len(pairs) else None, len(pairs)))
         self.navoid = len(pairs)
+        self.involved = set(x for a, b in avoid if a != b for x in (a, b))
         self.table = None
         self.sparse = None
         return idx
@@ -130,8 +131,6 @@ class Engine:
         """bed: uint8 CUDA tensor whose first byte starts a line.  Asynchronous."""
         assert bed.dtype == torch.uint8 and bed.is_cuda and bed.is_contiguous()
         st = torch.cuda.current_stream().cuda_stream
-        if self.navoid:
-            raise NotImplementedError('avoid-list ingest')
         if self.mode == 'dense':
             check(self.L.salsa_bed_ingest_dense(self.ctx, bed.data_ptr(), bed.numel(), base_offset,
                                                 self.table.data_ptr(), self.stats.data_ptr(), st))
@@ -179,8 +178,19 @@ class Engine:
                 nl = np.flatnonzero(blk[::-1][:4 * 1024 * 1024] == 10)      # newlines near the chunk's end
                 if len(nl) < 2:
                     raise ValueError('BED line longer than the staging chunk near byte %d' % pos)
-                end = pos + (len(blk) - 1 - int(nl[0])) + 1
-                nxt = pos + (len(blk) - 1 - int(nl[1])) + 1
+                k = 0
+                if self.navoid:
+                    # the next chunk must start on a line that can never be skipped: contig in no avoid pair
+                    while True:
+                        if k + 1 >= len(nl):
+                            raise ValueError('no line outside the avoid list near byte %d to split the BED at' % pos)
+                        ls = len(blk) - 1 - int(nl[k + 1]) + 1                # start of the last complete line
+                        tok = bytes(blk[ls:ls + 1024]).split(None, 1)
+                        if not tok or tok[0] not in self.involved:
+                            break
+                        k += 1
+                end = pos + (len(blk) - 1 - int(nl[k])) + 1
+                nxt = pos + (len(blk) - 1 - int(nl[k + 1])) + 1
             dev = torch.from_numpy(np.ascontiguousarray(mm[pos:end])).to(self.device)
             self.ingest_device(dev, base_offset=pos)
             torch.cuda.current_stream().synchronize()
