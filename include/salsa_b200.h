@@ -178,6 +178,26 @@ int salsa_sort_pairs_u64(uint64_t *d_keys_in, uint64_t *d_vals_in, uint64_t *d_k
                          uint64_t *d_vals_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream);
 
 /*
+ * Multi-GPU merge of per-GPU link tables (no counterpart in the
+ * single-process reference; the link key space is what make_links.py:140-144
+ * counts into).  Read pairs shard by BED byte range, so every GPU holds
+ * partial counts for arbitrary keys:
+ *   dense tables : one all-reduce (sum) of the uint64 table;
+ *   sparse tables: salsa_links_compact, then salsa_links_partition buckets the
+ *       (key, count) pairs by owner = mix64(key) % nparts (h_part_counts =
+ *       send counts of the all-to-all; d_scratch = 64 uint64), the caller
+ *       exchanges them (NCCL all-to-all), and salsa_sparse_add adds the
+ *       received pairs into the owner's table (*d_full_flag becomes 1 when the
+ *       table has no free slot).
+ * Integer sums: the merged result does not depend on the number of shards.
+ */
+int salsa_links_partition(const uint64_t *d_keys, const uint64_t *d_counts, size_t n, int32_t nparts,
+                          uint64_t *d_out_keys, uint64_t *d_out_counts, uint64_t *d_scratch,
+                          uint64_t *h_part_counts, void *stream);
+int salsa_sparse_add(const uint64_t *d_in_keys, const uint64_t *d_in_counts, size_t n, uint64_t *d_keys,
+                     uint64_t *d_counts, size_t capacity, uint32_t *d_full_flag, void *stream);
+
+/*
  * Python-2 str(float) on the device.  The reference passes scores between
  * programs as text written with str(float) = '%.12g' (make_links.py:169,
  * fast_scaled_scores.py:86; 12 digits evidenced by fast_scaled_scores.py:39-40),

@@ -150,6 +150,111 @@ extern "C" int salsa_links_compact(const uint64_t *d_keys, const uint64_t *d_cou
     return SALSA_OK;
 }
 
+// ---- multi-GPU merge of sparse tables ---------------------------------------
+// owner(key) = mix64(key) % nparts.  Links are bucketed by owner (histogram, scan,
+// scatter), exchanged with one all-to-all, and added into the receiver's table.
+namespace {
+
+constexpr int MAXPARTS = 64;
+
+__global__ void __launch_bounds__(256) part_count_kernel(const uint64_t *keys, size_t n, int nparts, unsigned long long *pcount)
+{
+    __shared__ unsigned int h[MAXPARTS];
+    if (threadIdx.x < MAXPARTS) h[threadIdx.x] = 0;
+    __syncthreads();
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) atomicAdd(&h[salsa_mix64(keys[i]) % (uint64_t)nparts], 1u);
+    __syncthreads();
+    if (threadIdx.x < nparts && h[threadIdx.x]) atomicAdd(&pcount[threadIdx.x], (unsigned long long)h[threadIdx.x]);
+}
+
+// cursor[p] starts at the exclusive prefix of pcount; each block reserves its share per part
+__global__ void __launch_bounds__(256) part_scatter_kernel(const uint64_t *keys, const uint64_t *counts, size_t n, int nparts,
+                                                          unsigned long long *cursor, uint64_t *okeys, uint64_t *ocounts)
+{
+    __shared__ unsigned int h[MAXPARTS];
+    __shared__ unsigned long long base[MAXPARTS];
+    size_t per = (n + gridDim.x - 1) / gridDim.x;
+    size_t lo = (size_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
+    if (threadIdx.x < MAXPARTS) h[threadIdx.x] = 0;
+    __syncthreads();
+    for (size_t i = lo + threadIdx.x; i < hi; i += blockDim.x) atomicAdd(&h[salsa_mix64(keys[i]) % (uint64_t)nparts], 1u);
+    __syncthreads();
+    if (threadIdx.x < nparts) {
+        base[threadIdx.x] = h[threadIdx.x] ? atomicAdd(&cursor[threadIdx.x], (unsigned long long)h[threadIdx.x]) : 0ull;
+        h[threadIdx.x] = 0;
+    }
+    __syncthreads();
+    for (size_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        uint64_t k = keys[i];
+        int p = (int)(salsa_mix64(k) % (uint64_t)nparts);
+        unsigned long long o = base[p] + atomicAdd(&h[p], 1u);
+        okeys[o] = k;
+        ocounts[o] = counts[i];
+    }
+}
+
+__global__ void sparse_add_kernel(const uint64_t *ikeys, const uint64_t *icounts, size_t n, uint64_t *keys, uint64_t *counts,
+                                  uint64_t cap_mask, unsigned int *full)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t key = ikeys[i];
+    uint64_t slot = salsa_mix64(key) & cap_mask;
+    for (uint64_t probe = 0; probe <= cap_mask; probe++) {
+        unsigned long long k = ((volatile unsigned long long *)keys)[slot];
+        if (k == ~0ull) {
+            unsigned long long old = atomicCAS((unsigned long long *)&keys[slot], ~0ull, (unsigned long long)key);
+            k = (old == ~0ull || old == key) ? key : old;
+        }
+        if (k == key) {
+            atomicAdd((unsigned long long *)&counts[slot], (unsigned long long)icounts[i]);
+            return;
+        }
+        slot = (slot + 1) & cap_mask;
+    }
+    atomicExch(full, 1u);
+}
+
+}   // namespace
+
+extern "C" int salsa_links_partition(const uint64_t *d_keys, const uint64_t *d_counts, size_t n, int32_t nparts,
+                                     uint64_t *d_out_keys, uint64_t *d_out_counts, uint64_t *d_scratch, uint64_t *h_part_counts,
+                                     void *stream)
+{
+    if (nparts < 1 || nparts > MAXPARTS) SALSA_FAIL(SALSA_ERR_ARG, "salsa_links_partition: 1..%d parts", MAXPARTS);
+    if (!h_part_counts || !d_scratch || (n && (!d_keys || !d_counts || !d_out_keys || !d_out_counts)))
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_links_partition: NULL argument");
+    cudaStream_t st = as_stream(stream);
+    unsigned long long *pc = (unsigned long long *)d_scratch;          // [nparts] counts, then cursors
+    CUDA_TRY(cudaMemsetAsync(pc, 0, MAXPARTS * sizeof(uint64_t), st));
+    unsigned grid = n ? (unsigned)((n + 256 * 16 - 1) / (256 * 16)) : 1;
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (n) part_count_kernel<<<grid, 256, 0, st>>>(d_keys, n, nparts, pc);
+    CUDA_TRY(cudaMemcpyAsync(h_part_counts, pc, (size_t)nparts * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    uint64_t cur[MAXPARTS], acc = 0;
+    for (int p = 0; p < nparts; p++) { cur[p] = acc; acc += h_part_counts[p]; }
+    CUDA_TRY(cudaMemcpyAsync(pc, cur, (size_t)nparts * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    if (n) part_scatter_kernel<<<grid, 256, 0, st>>>(d_keys, d_counts, n, nparts, pc, d_out_keys, d_out_counts);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(st));       // `cur` lives on this stack frame
+    return SALSA_OK;
+}
+
+extern "C" int salsa_sparse_add(const uint64_t *d_in_keys, const uint64_t *d_in_counts, size_t n, uint64_t *d_keys,
+                                uint64_t *d_counts, size_t capacity, uint32_t *d_full_flag, void *stream)
+{
+    if (n == 0) return SALSA_OK;
+    if (!d_in_keys || !d_in_counts || !d_keys || !d_counts || !d_full_flag || capacity == 0 || (capacity & (capacity - 1)))
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_sparse_add: bad argument");
+    sparse_add_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(d_in_keys, d_in_counts, n, d_keys, d_counts,
+                                                                                   capacity - 1, d_full_flag);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
 // key-sorts (key, count) pairs; used after compacting a sparse table.  The
 // radix sort is CUB's (library code: this step is off the hot path).
 extern "C" int salsa_sort_pairs_u64(uint64_t *d_keys_in, uint64_t *d_vals_in, uint64_t *d_keys_out, uint64_t *d_vals_out,

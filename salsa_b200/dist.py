@@ -1,0 +1,156 @@
+"""Multi-GPU plumbing of the link-table path: one process per GPU, torch.distributed
+(NCCL over NVLink / NVSwitch on the GPU box, gloo in the CPU tests).
+
+The data path shards naturally -- read pairs are independent -- so the only
+exchange step is the merge of the per-GPU tables:
+  dense  : all-reduce(sum) of the uint64 table (288 MB for 3,000 contigs);
+  sparse : hash-partition the compacted (key, count) pairs on the key, one
+           all-to-all, then add into the owner's table.
+Integer sums: results do not depend on the number of shards.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_ranges(view, world):
+    """Cut a BED (anything indexable as bytes: bytes, np.memmap, ...) into `world`
+    byte ranges that start on line starts and overlap by exactly one line, the
+    chunking rule of salsa_bed_ingest_dense (include/salsa_b200.h): shard k's first
+    line is shard k-1's last line, which only plays "previous"
+    (make_links.py:66-68), so every adjacent-line pair is evaluated exactly once.
+    Returns [(lo, hi)] * world; empty shards are (hi, hi)."""
+    n = len(view)
+    if n == 0:
+        return [(0, 0)] * world
+
+    def line_start_at_or_before(p):
+        # start of the line that contains byte p
+        lo = max(0, p - (1 << 20))
+        blk = np.frombuffer(bytes(view[lo:p]), dtype=np.uint8) if p > lo else np.zeros(0, np.uint8)
+        nl = np.flatnonzero(blk == 10)
+        if len(nl):
+            return lo + int(nl[-1]) + 1
+        if lo == 0:
+            return 0
+        raise ValueError('BED line longer than 1 MiB near byte %d' % p)
+
+    cuts = [0]
+    for k in range(1, world):
+        p = n * k // world
+        cuts.append(max(cuts[-1], line_start_at_or_before(min(p, n - 1))))
+    ranges = []
+    for k in range(world):
+        lo = cuts[k]
+        if k + 1 < world:
+            nxt = cuts[k + 1]
+            # shard k ends after the line that STARTS at cuts[k+1] (that line is shared)
+            blk = np.frombuffer(bytes(view[nxt:min(n, nxt + (1 << 20))]), dtype=np.uint8)
+            nl = np.flatnonzero(blk == 10)
+            hi = nxt + int(nl[0]) + 1 if len(nl) else n
+        else:
+            hi = n
+        ranges.append((lo, hi) if hi > lo else (hi, hi))
+    return ranges
+
+
+def merge_dense(table):
+    """Sum the per-GPU dense tables in place on every rank."""
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(table)
+    return table
+
+
+class TorchOps:
+    """Reference implementations of the two device steps of the sparse merge with torch ops.
+    Used by the CPU (gloo) tests of the exchange plumbing; the GPU path uses EngineOps."""
+
+    @staticmethod
+    def mix64(x):
+        # must agree with salsa_mix64 (common.cuh); int64 arithmetic wraps like uint64
+        def shr(v, k):
+            return (v >> k) & ((1 << (64 - k)) - 1)
+        x = x ^ shr(x, 33)
+        x = x * torch.tensor(-49064778989728563, dtype=torch.int64)        # 0xff51afd7ed558ccd
+        x = x ^ shr(x, 33)
+        x = x * torch.tensor(-4265267296055464877, dtype=torch.int64)      # 0xc4ceb9fe1a85ec53
+        x = x ^ shr(x, 33)
+        return x
+
+    def partition(self, keys, counts, nparts):
+        h = self.mix64(keys)
+        # unsigned modulo of a wrapped int64
+        owner = torch.from_numpy((h.numpy().view(np.uint64) % np.uint64(nparts)).astype(np.int64))
+        order = torch.argsort(owner, stable=True)
+        pc = torch.bincount(owner, minlength=nparts)
+        return keys[order], counts[order], pc.tolist()
+
+    def reduce(self, keys, counts):
+        if keys.numel() == 0:
+            return keys, counts
+        uk, inv = torch.unique(keys, return_inverse=True)
+        out = torch.zeros(uk.numel(), dtype=counts.dtype)
+        out.index_add_(0, inv, counts)
+        return uk, out
+
+
+def exchange_sparse(keys, counts, ops, group=None):
+    """Hash-partitioned all-to-all of compacted (key, count) pairs followed by a local
+    reduce.  keys/counts: 1-D int64 tensors (device of the process group's backend).
+    Returns the (keys, counts) this rank OWNS, reduced."""
+    world = dist.get_world_size(group)
+    pk, pc, send = ops.partition(keys, counts, world)
+    send_t = torch.tensor(send, dtype=torch.int64, device=keys.device)
+    recv_t = torch.empty(world, dtype=torch.int64, device=keys.device)
+    dist.all_to_all_single(recv_t, send_t, group=group)
+    recv = [int(x) for x in recv_t.tolist()]
+    rk = torch.empty(sum(recv), dtype=torch.int64, device=keys.device)
+    rc = torch.empty(sum(recv), dtype=torch.int64, device=keys.device)
+    dist.all_to_all_single(rk, pk, output_split_sizes=recv, input_split_sizes=[int(x) for x in send], group=group)
+    dist.all_to_all_single(rc, pc, output_split_sizes=recv, input_split_sizes=[int(x) for x in send], group=group)
+    return ops.reduce(rk, rc)
+
+
+class EngineOps:
+    """The device steps of the sparse merge through the C ABI (salsa_links_partition,
+    salsa_sparse_add + salsa_links_compact)."""
+
+    def __init__(self, eng):
+        self.eng = eng
+
+    def partition(self, keys, counts, nparts):
+        import ctypes as C
+        from ._lib import check
+        L, dev = self.eng.L, self.eng.device
+        n = keys.numel()
+        ok = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+        oc = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+        scratch = torch.zeros(64, dtype=torch.int64, device=dev)
+        pc = (C.c_uint64 * nparts)()
+        check(L.salsa_links_partition(keys.data_ptr(), counts.data_ptr(), n, nparts, ok.data_ptr(), oc.data_ptr(),
+                                      scratch.data_ptr(), pc, torch.cuda.current_stream().cuda_stream))
+        return ok[:n], oc[:n], [int(x) for x in pc]
+
+    def reduce(self, keys, counts):
+        import ctypes as C
+        from ._lib import check
+        L, dev = self.eng.L, self.eng.device
+        st = torch.cuda.current_stream().cuda_stream
+        n = keys.numel()
+        cap = 1 << 10
+        while cap < 2 * n + 2:
+            cap <<= 1
+        tk = torch.empty(cap, dtype=torch.int64, device=dev)
+        tc = torch.empty(cap, dtype=torch.int64, device=dev)
+        check(L.salsa_sparse_reset(tk.data_ptr(), tc.data_ptr(), cap, st))
+        full = torch.zeros(1, dtype=torch.int32, device=dev)
+        check(L.salsa_sparse_add(keys.data_ptr(), counts.data_ptr(), n, tk.data_ptr(), tc.data_ptr(), cap, full.data_ptr(), st))
+        assert int(full.item()) == 0
+        scratch = torch.empty(L.salsa_links_compact_scratch_bytes(cap) // 8 + 1, dtype=torch.int64, device=dev)
+        m = C.c_uint64(0)
+        check(L.salsa_links_compact(tk.data_ptr(), tc.data_ptr(), cap, None, None, 0, scratch.data_ptr(), C.byref(m), st))
+        ok = torch.empty(max(m.value, 1), dtype=torch.int64, device=dev)
+        oc = torch.empty(max(m.value, 1), dtype=torch.int64, device=dev)
+        check(L.salsa_links_compact(tk.data_ptr(), tc.data_ptr(), cap, ok.data_ptr(), oc.data_ptr(), m.value, scratch.data_ptr(),
+                                    C.byref(m), st))
+        return ok[:m.value], oc[:m.value]
