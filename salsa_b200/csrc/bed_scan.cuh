@@ -34,7 +34,7 @@ namespace bedscan {
 #define SALSA_TILE 32768
 #endif
 #ifndef SALSA_MINBLOCKS
-#define SALSA_MINBLOCKS 3
+#define SALSA_MINBLOCKS 4
 #endif
 constexpr int TILE = SALSA_TILE;
 constexpr int HALO = SALSA_MAX_LINE;   // 1024
@@ -364,6 +364,22 @@ __device__ __forceinline__ bool same_contig(const uint8_t *s, const Rec &pv, con
     return pl == cl && bytes_equal_back(s, pv.name & 0xFFFF, cu.name & 0xFFFF, cl);
 }
 
+__device__ __forceinline__ Rec rec_shfl_idx(const Rec &r, int src)
+{
+    Rec o;
+    o.id = __shfl_sync(0xffffffffu, r.id, src);
+    o.s_lo = __shfl_sync(0xffffffffu, r.s_lo, src);
+    o.s_hi = __shfl_sync(0xffffffffu, r.s_hi, src);
+    o.e_lo = __shfl_sync(0xffffffffu, r.e_lo, src);
+    o.e_hi = __shfl_sync(0xffffffffu, r.e_hi, src);
+    o.name = __shfl_sync(0xffffffffu, r.name, src);
+    o.read = __shfl_sync(0xffffffffu, r.read, src);
+    o.flags = __shfl_sync(0xffffffffu, r.flags, src);
+#pragma unroll
+    for (int j = 0; j < RW; j++) o.rw[j] = __shfl_sync(0xffffffffu, r.rw[j], src);
+    return o;
+}
+
 __device__ __forceinline__ Rec rec_shfl_up(const Rec &r)
 {
     Rec o;
@@ -476,7 +492,7 @@ __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
 // Process the lines whose first byte lies in (lo, hi] (abase coordinates).
 // sb: abase coordinate of smem byte 0.  WRITE_SP: also fill the special bitmap
 // of the scanned chunks (the full-tile call; sub-range calls reuse it).
-template <class Policy, bool WRITE_SP>
+template <class Policy, bool WRITE_SP, bool WARP_AUTONOMOUS>
 __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A, const Smem &S, long long sb, long long lo,
                               long long hi, long long l0, int sent, bool trunc, uint32_t &nlines_acc, uint32_t &npairs_acc)
 {
@@ -542,6 +558,67 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     }
     __syncthreads();
     if (*S.flagp) return;                // only from the full-tile call; the caller falls back to subtiles
+    if (WARP_AUTONOMOUS) {
+        // Each warp parses and pairs the lines that START in its own 1/8 of the range, 32 per step.
+        // No block barrier, no line-list compaction: the record of a step's last lane reaches the
+        // next step by shuffle, and a warp's very first "previous" line is the last line start of
+        // the nearest non-empty warp before it (or found by the backward search below).
+        if (cnt == 0) return;
+        const uint16_t *my = S.seg + warp * WCAP;
+        int prev_start;
+        {
+            int v = warp - 1;
+            while (v >= 0 && S.wcount[v] == 0) v--;
+            if (v >= 0) prev_start = S.seg[v * WCAP + S.wcount[v] - 1];
+            else {
+                long long lowpos = l0 > (long long)A.mis ? l0 : (long long)A.mis;
+                int low = (int)(lowpos - sb);
+                int first = my[0], found = -1;
+                for (int base = first - 2; base >= low && found < 0; base -= 32) {
+                    int idx = base - lane;
+                    bool hit = idx >= low && s[idx] == '\n';
+                    unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (m) found = base - (__ffs(m) - 1);
+                }
+                if (found >= 0) prev_start = found + 1;
+                else {
+                    prev_start = low;                // first line of the buffer, or a line longer than the halo
+                    if (lowpos != (long long)A.mis && lane == 0)
+                        report(A.stats, A.base_offset + (uint64_t)(lowpos - A.mis), SALSA_DATA_LINE_TOO_LONG);
+                }
+            }
+        }
+        const int first_line_idx = (int)((long long)A.mis - sb);
+        Rec last;
+        last.id = -1; last.s_lo = last.s_hi = last.e_lo = last.e_hi = 0; last.name = last.read = 0; last.flags = 0;
+#pragma unroll
+        for (int j = 0; j < RW; j++) last.rw[j] = 0;
+        int last_start = -2;
+        for (int k0 = -1; k0 < cnt; k0 += 32) {
+            int k = k0 + lane;                       // entry -1 is the previous line, entries 0..cnt-1 are owned
+            Rec rec;
+            rec.id = -1; rec.s_lo = rec.s_hi = rec.e_lo = rec.e_hi = 0; rec.name = rec.read = 0; rec.flags = 0;
+#pragma unroll
+            for (int j = 0; j < RW; j++) rec.rw[j] = 0;
+            int lstart = 0;
+            if (k < cnt) {
+                lstart = k < 0 ? prev_start : (int)my[k];
+                rec = parse_any<Policy>(A, S, lstart, sent, trunc, true);
+            }
+            Rec pv = rec_shfl_up(rec);
+            int pstart = __shfl_up_sync(0xffffffffu, lstart, 1);
+            if (lane == 0) { pv = last; pstart = last_start; }
+            if (k >= 0 && k < cnt) {
+                nlines_acc++;
+                uint64_t off = A.base_offset + (uint64_t)((long long)lstart + sb - (long long)A.mis);
+                bool prev_is_first = sb <= 0 && pstart == first_line_idx;
+                if (Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
+            }
+            last = rec_shfl_idx(rec, 31);
+            last_start = __shfl_sync(0xffffffffu, lstart, 31);
+        }
+        return;
+    }
     int wb = 0, n = 0;
 #pragma unroll
     for (int w = 0; w < NWARPS; w++) {
@@ -749,7 +826,8 @@ __global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typ
         }
     }
     uint32_t nlines = 0, npairs = 0;
-    process_range<Policy, true>(PA, A, S, sb, t0, hi, l0, sent, trunc, nlines, npairs);
+    // avoid mode needs the block-wide line list (its walk-back crosses warp regions)
+    process_range<Policy, true, !Policy::AVOID>(PA, A, S, sb, t0, hi, l0, sent, trunc, nlines, npairs);
     if (*S.flagp) {
         // > WCAP line starts inside one warp's 4 KB: redo the tile in 2 KB ranges,
         // which cannot overflow (a line start needs at least one byte)
@@ -760,7 +838,7 @@ __global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typ
             if (tid == 0) *S.flagp = 0;
             __syncthreads();
             long long h2 = lo + SUBTILE < hi ? lo + SUBTILE : hi;
-            process_range<Policy, false>(PA, A, S, sb, lo, h2, l0, sent, trunc, nlines, npairs);
+            process_range<Policy, false, false>(PA, A, S, sb, lo, h2, l0, sent, trunc, nlines, npairs);
         }
     }
     // ---- statistics: one atomic pair per CTA -----------------------------
