@@ -222,6 +222,9 @@ def run_ours(args):
            'sample': 'first %d bytes of the same BED from pinned host memory via salsa_bed_ingest_dense_host '
                      '(64 MiB double-buffered chunks) + D2H of the compacted link list' % cut}
 
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     peak, which = peaks()
@@ -239,7 +242,7 @@ def run_ours(args):
                    'parity_full_size': 'table == generator expected table: %s; counted pairs %d' % (parity, stt.pairs)},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'traffic': None, 'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
-                     'kernel': 'bed_ingest_kernel<dense>', 'algorithmic_bytes_per_launch': bed_bytes,
+                     'kernel': 'bedscan::bed_scan_kernel<LinkPolicy<dense>>', 'algorithmic_bytes_per_launch': bed_bytes,
                      'kernel_ms': kern_ms},
         'e2e': e2e,
         'gpu_launches': args.steps * 1,

@@ -33,19 +33,44 @@ def expand_enzymes(enzyme):
     return out
 
 
-def count_sites(eng, fasta, enzyme):
-    """fasta: host uint8 numpy array (np.memmap works).  Returns (names, left, right,
-    seqlen) in first-appearance order of record names; a repeated name keeps its
-    first position and its last sequence (dict assignment, RE_sites.py:19)."""
+class _DeviceView:
+    """Byte access to a FASTA that lives only in device memory (bench / pipelines that keep it in HBM)."""
+
+    def __init__(self, t):
+        self.t = t
+        self.size = t.numel()
+
+    def __getitem__(self, key):
+        return self.t[key].cpu().numpy()
+
+
+def count_sites(eng, fasta, enzyme, timers=None):
+    """fasta: host uint8 numpy array (np.memmap works) or a uint8 CUDA tensor.  Returns
+    (names, left, right, seqlen) in first-appearance order of record names; a repeated
+    name keeps its first position and its last sequence (dict assignment, RE_sites.py:19).
+    timers: optional dict that receives (start, end) CUDA event pairs per stage."""
     L, dev = eng.L, eng.device
     st = torch.cuda.current_stream().cuda_stream
+    d = None
+    if isinstance(fasta, torch.Tensor):
+        d = fasta
+        fasta = _DeviceView(d)
     n = int(fasta.size)
     if n == 0:
         return [], np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0, np.int64)
-    if fasta[0] != ord('>'):
+    if fasta[0:1][0] != ord('>'):
         raise FastaError('sequence line before the first header (the reference raises KeyError, RE_sites.py:22)')
     patterns = None if enzyme == 'DNASE' else expand_enzymes(enzyme)          # validate before any GPU work
-    d = torch.from_numpy(np.ascontiguousarray(fasta)).to(dev)
+    if d is None:
+        d = torch.from_numpy(np.array(fasta, copy=True) if not fasta.flags.writeable else np.ascontiguousarray(fasta)).to(dev)
+
+    def tick(name):
+        if timers is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            timers.setdefault(name, []).append(ev)
+
+    tick('headers')
     cap = 1 << 16
     while True:
         pos = torch.empty(cap, dtype=torch.int64, device=dev)
@@ -55,6 +80,7 @@ def count_sites(eng, fasta, enzyme):
         if k <= cap:
             break
         cap = k
+    tick('headers')
     hp = np.sort(pos[:k].cpu().numpy())
     names, sbeg, send = [], np.zeros(k, np.uint64), np.zeros(k, np.uint64)
     for i, p in enumerate(hp):
@@ -82,12 +108,14 @@ def count_sites(eng, fasta, enzyme):
     err = torch.zeros(1, dtype=torch.int32, device=dev)
     nt = L.salsa_fasta_tiles(n)
     tiles = torch.zeros(nt + 1, dtype=torch.int64, device=dev)
+    tick('count')
     check(L.salsa_fasta_count(d.data_ptr(), n, dsb.data_ptr(), dse.data_ptr(), k, tiles.data_ptr(), err.data_ptr(), st))
     check(L.salsa_exclusive_scan_u64(tiles.data_ptr(), nt, st))
     pbeg = torch.zeros(k, dtype=torch.int64, device=dev)
     plen = torch.zeros(k, dtype=torch.int64, device=dev)
     check(L.salsa_fasta_span_lengths(d.data_ptr(), n, dsb.data_ptr(), dse.data_ptr(), k, tiles.data_ptr(), pbeg.data_ptr(),
                                      plen.data_ptr(), err.data_ptr(), st))
+    tick('count')
     seqlen = plen.cpu().numpy()
     if int(err.item()):
         raise FastaError('a run of trailing whitespace longer than 1024 bytes (library limit)')
@@ -100,16 +128,22 @@ def count_sites(eng, fasta, enzyme):
         nblk = int(blk[-1])
         dblk = torch.from_numpy(blk).to(dev)
         planes = torch.zeros(max(3 * nblk, 1), dtype=torch.int64, device=dev)
+        tick('pack')
         check(L.salsa_fasta_pack(d.data_ptr(), n, dsb.data_ptr(), dse.data_ptr(), k, tiles.data_ptr(), pbeg.data_ptr(),
                                  dblk.data_ptr(), planes.data_ptr(), err.data_ptr(), st))
+        tick('pack')
         dl = torch.zeros(k, dtype=torch.int64, device=dev)
         dr = torch.zeros(k, dtype=torch.int64, device=dev)
         nborder = sum(1 for p in patterns if any(p[:j] == p[-j:] for j in range(1, len(p))))
         occ = torch.zeros(max(nborder * nblk, 1), dtype=torch.int64, device=dev) if nborder else None
         blob = b''.join(p.encode() + b'\0' for p in patterns)
+        tick('re_count')
         check(L.salsa_re_count(planes.data_ptr(), dblk.data_ptr(), plen.data_ptr(), k, nblk, blob, len(patterns), dl.data_ptr(),
                                dr.data_ptr(), occ.data_ptr() if occ is not None else None, st))
+        tick('re_count')
         left, right = dl.cpu().numpy(), dr.cpu().numpy()
+        if timers is not None:
+            timers['_sizes'] = dict(fasta_bytes=n, bases=int(seqlen.sum()), plane_bytes=int(nblk) * 24, npatterns=len(patterns))
     # dict semantics: first position, last value
     order, last = [], {}
     for i, nm in enumerate(names):
