@@ -61,7 +61,7 @@ struct CovPolicy {
         if (cu.id < 0) return false;                               // contig_length[unknown] == 0 < 1000000
         const uint64_t base = C.covoff[cu.id];
         if (base == ~0ull) return false;                           // :325 / :218
-        C.touched[cu.id] = 1;                                      // :333-337 / :226-230
+        if (!C.touched[cu.id]) C.touched[cu.id] = 1;               // :333-337 / :226-230 (read first: no store storm on a hot line)
         if (C.first_chunk && prev_is_first) return false;          // the first line is never parsed: prev_* are still initial
         if ((pv.flags & 7u) < 4u || (pv.flags & 8u)) return false; // after a malformed line nothing counts (rerun truncates)
         if (pv.id != cu.id) return false;                          // prev_contig == contig

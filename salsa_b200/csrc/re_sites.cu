@@ -63,13 +63,54 @@ __device__ __forceinline__ int span_of(const Spans &S, unsigned long long p)
     return lo - 1;
 }
 
+// Spans that can intersect one tile (+ halo), cached in shared memory: a per-byte binary
+// search over the global span table would cost a dozen dependent global loads per byte.
+constexpr int SC = 16;
+struct SpanCache {
+    int r0, n;                       // first cached span index; n < 0: too many spans in this tile, search globally
+    unsigned long long beg[SC], end[SC];
+};
+
+__device__ void span_cache_fill(const Spans &S, size_t t0, size_t t1, SpanCache *c)
+{
+    int r = span_of(S, t0);
+    if (r < 0) r = 0;
+    c->r0 = r;
+    int k = 0;
+    while (r < S.nspan && S.sbeg[r] < t1) {
+        if (k == SC) { k = -1; break; }
+        c->beg[k] = S.sbeg[r];
+        c->end[k] = S.send[r];
+        k++; r++;
+    }
+    c->n = k;
+}
+
+// span containing-or-preceding p: returns its index (or -1) and its end
+__device__ __forceinline__ int span_find(const Spans &S, const SpanCache &c, unsigned long long p, unsigned long long *e)
+{
+    if (c.n < 0) {
+        int r = span_of(S, p);
+        *e = r >= 0 ? S.send[r] : 0;
+        return r;
+    }
+    int hit = -1;
+    for (int i = 0; i < c.n; i++)
+        if (c.beg[i] <= p) hit = i;
+    if (hit < 0) { *e = 0; return -1; }
+    *e = c.end[hit];
+    return c.r0 + hit;
+}
+
 // Stage [t0, t0 + FT + FHALO) of the text into smem and compute, for the tile's
 // FT bytes, kept flags (1 byte each, in `kept`).  Returns via *err when a
 // whitespace run cannot be resolved inside the halo.
-__device__ void tile_kept(const uint8_t *txt, size_t n, const Spans &S, size_t t0, uint8_t *sm, uint8_t *kept, int *err)
+__device__ void tile_kept(const uint8_t *txt, size_t n, const Spans &S, size_t t0, uint8_t *sm, uint8_t *kept, int *err,
+                          SpanCache *sc)
 {
     const int tid = threadIdx.x;
     const int tot = FT + FHALO;
+    if (tid == 0) span_cache_fill(S, t0, t0 + tot, sc);
     for (int i = tid; i < tot; i += FTHREADS) {
         size_t p = t0 + i;
         sm[i] = p < n ? txt[p] : (uint8_t)'\n';
@@ -80,14 +121,15 @@ __device__ void tile_kept(const uint8_t *txt, size_t n, const Spans &S, size_t t
         size_t p = t0 + i;
         uint8_t k = 0;
         if (p < n) {
-            int r = span_of(S, p);
-            if (r >= 0 && p < S.send[r]) {
+            unsigned long long send_r;
+            int r = span_find(S, *sc, p, &send_r);
+            if (r >= 0 && p < send_r) {
                 uint32_t c = sm[i];
                 if (c != '\n') {
                     k = 1;
                     if (is_ws_b(c)) {
                         // trailing iff only whitespace until the next '\n' or the span end
-                        size_t e = S.send[r];
+                        size_t e = send_r;
                         int j = i + 1;
                         for (;;) {
                             size_t q = t0 + j;
@@ -113,7 +155,8 @@ __global__ void __launch_bounds__(FTHREADS) fasta_count_kernel(const uint8_t *tx
     __shared__ uint8_t kept[FT];
     __shared__ int red[FTHREADS / 32];
     size_t t0 = (size_t)blockIdx.x * FT;
-    tile_kept(txt, n, S, t0, sm, kept, err);
+    __shared__ SpanCache sc;
+    tile_kept(txt, n, S, t0, sm, kept, err, &sc);
     int c = 0;
     for (int i = threadIdx.x; i < FT; i += FTHREADS) c += kept[i];
 #pragma unroll
@@ -135,6 +178,7 @@ __global__ void __launch_bounds__(FTHREADS) span_prefix_kernel(const uint8_t *tx
     __shared__ uint8_t sm[FT + FHALO];
     __shared__ uint8_t kept[FT];
     __shared__ int red[FTHREADS / 32];
+    __shared__ SpanCache sc;
     int r = blockIdx.x;
     uint64_t res[2];
     for (int which = 0; which < 2; which++) {
@@ -144,7 +188,7 @@ __global__ void __launch_bounds__(FTHREADS) span_prefix_kernel(const uint8_t *tx
         int upto = (int)(p - t0);
         int c = 0;
         if (upto > 0) {
-            tile_kept(txt, n, S, t0, sm, kept, err);
+            tile_kept(txt, n, S, t0, sm, kept, err, &sc);
             for (int i = threadIdx.x; i < upto; i += FTHREADS) c += kept[i];
         }
 #pragma unroll
@@ -174,7 +218,8 @@ __global__ void __launch_bounds__(FTHREADS) fasta_pack_kernel(const uint8_t *txt
     __shared__ int wtot[FTHREADS / 32 + 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     size_t t0 = (size_t)blockIdx.x * FT;
-    tile_kept(txt, n, S, t0, sm, kept, err);
+    __shared__ SpanCache sc;
+    tile_kept(txt, n, S, t0, sm, kept, err, &sc);
     // each thread owns 16 consecutive bytes; block-wide exclusive scan of kept counts
     int c = 0;
     const int per = FT / FTHREADS;      // 16
@@ -200,34 +245,37 @@ __global__ void __launch_bounds__(FTHREADS) fasta_pack_kernel(const uint8_t *txt
         if (!kept[i]) continue;
         uint32_t ch = sm[i];
         uint32_t cd = ch == 'A' ? 4u : ch == 'C' ? 5u : ch == 'G' ? 6u : ch == 'T' ? 7u : 0u;   // valid<<2 | code
-        int r = span_of(S, t0 + i);
+        unsigned long long dummy;
+        int r = span_find(S, sc, t0 + i, &dummy);
         code[pos] = (uint8_t)cd;
         opos[pos] = (unsigned long long)(blk_off[r] * 64ull + (tbase + (uint64_t)pos - pbeg[r]));
         pos++;
     }
     __syncthreads();
     const int k = wtot[FTHREADS / 32];
-    // group compacted bytes by output 64-base block: thread i handles byte i if it is the
-    // first of its block inside this tile, then gathers the run (<= 64 bytes)
-    for (int i = tid; i < k; i += FTHREADS) {
-        unsigned long long o = opos[i];
-        bool first = i == 0 || (opos[i - 1] >> 6) != (o >> 6) || opos[i - 1] + 1 != o;
-        if (!first) continue;
-        unsigned long long hi = 0, lo = 0, va = 0;
-        int j = i;
+    // one compacted byte per lane: lanes that fall into the same output 64-base block
+    // (__match_any_sync) OR their bits together with warp reductions and the group's first
+    // lane issues the atomics.  Blocks are shared with neighbouring warps / tiles, hence
+    // atomicOr into zero-initialised planes.
+    for (int base = 0; base < k; base += FTHREADS) {
+        int i = base + tid;
+        bool act = i < k;
+        unsigned long long o = act ? opos[i] : ~0ull;
         unsigned long long blk = o >> 6;
-        while (j < k && (opos[j] >> 6) == blk && (j == i || opos[j] == opos[j - 1] + 1)) {
-            unsigned long long bit = 1ull << (opos[j] & 63);
-            uint32_t cd = code[j];
-            if (cd & 2u) hi |= bit;
-            if (cd & 1u) lo |= bit;
-            if (cd & 4u) va |= bit;
-            j++;
+        uint32_t cd = act ? code[i] : 0u;
+        int b = (int)(o & 63);
+        unsigned grp = __match_any_sync(0xffffffffu, blk);
+        uint32_t blo = b < 32 ? (1u << b) : 0u, bhi = b >= 32 ? (1u << (b - 32)) : 0u;
+        uint32_t h0 = __reduce_or_sync(grp, (cd & 2u) ? blo : 0u), h1 = __reduce_or_sync(grp, (cd & 2u) ? bhi : 0u);
+        uint32_t l0 = __reduce_or_sync(grp, (cd & 1u) ? blo : 0u), l1 = __reduce_or_sync(grp, (cd & 1u) ? bhi : 0u);
+        uint32_t v0 = __reduce_or_sync(grp, (cd & 4u) ? blo : 0u), v1 = __reduce_or_sync(grp, (cd & 4u) ? bhi : 0u);
+        if (act && lane == __ffs(grp) - 1) {
+            unsigned long long hi = ((unsigned long long)h1 << 32) | h0, lo = ((unsigned long long)l1 << 32) | l0;
+            unsigned long long va = ((unsigned long long)v1 << 32) | v0;
+            if (hi) atomicOr(&planes[blk * 3 + 0], hi);
+            if (lo) atomicOr(&planes[blk * 3 + 1], lo);
+            if (va) atomicOr(&planes[blk * 3 + 2], va);
         }
-        // partial blocks are shared with neighbouring tiles: OR into zero-initialised planes
-        if (hi) atomicOr(&planes[blk * 3 + 0], hi);
-        if (lo) atomicOr(&planes[blk * 3 + 1], lo);
-        if (va) atomicOr(&planes[blk * 3 + 2], va);
     }
 }
 
