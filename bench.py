@@ -29,6 +29,23 @@ METRIC = 'hic_pairs_per_sec_into_link_table'
 UNIT = 'pairs/s'
 
 
+def ncu_traffic_ratio():
+    """dram bytes (read + write) / algorithmic bytes of the ingest kernel, from the committed
+    `ncu --set full` capture (profiles/r01_v2_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
+    p = os.path.join(ROOT, 'profiles', 'r01_v2_ingest_metrics.txt')
+    try:
+        rd = wr = None
+        for ln in open(p):
+            a = ln.split()
+            if a and a[0] == 'dram__bytes_read.sum':
+                rd = float(a[2]) * {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}[a[1]]
+            if a and a[0] == 'dram__bytes_write.sum':
+                wr = float(a[2]) * {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}[a[1]]
+        return (rd + wr) / 4703357292.0
+    except Exception:
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(p):
@@ -241,7 +258,10 @@ def run_ours(args):
                    'parallelism': 'read pairs sharded over %d GPU(s); NCCL all-reduce of the dense table' % world,
                    'parity_full_size': 'table == generator expected table: %s; counted pairs %d' % (parity, stt.pairs)},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                     'traffic': None, 'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
+                     'traffic': (ncu_traffic_ratio() * bed_bytes) if ncu_traffic_ratio() else None,
+                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r01_v2_ingest_metrics.txt), '
+                                       'scaled to this launch by algorithmic bytes',
+                     'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
                      'kernel': 'bedscan::bed_scan_kernel<LinkPolicy<dense>>', 'algorithmic_bytes_per_launch': bed_bytes,
                      'kernel_ms': kern_ms},
         'e2e': e2e,
