@@ -87,7 +87,7 @@ t = torch.full((64,), r + 1, dtype=torch.int64)
 merge_dense(t)
 assert int(t[0]) == sum(range(1, w + 1))
 dist.destroy_process_group()
-print('rank', r, 'ok')
+sys.stdout.write('rank %%d ok\n' %% r)     # one write per rank: no interleaving
 '''
 
 

@@ -84,7 +84,7 @@ for p in parts:
 assert merged == want
 dist.barrier()
 dist.destroy_process_group()
-print('rank', rank, 'ok')
+sys.stdout.write('rank %%d ok\n' %% rank)     # one write per rank: no interleaving
 '''
 
 
