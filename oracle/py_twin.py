@@ -233,3 +233,133 @@ def re_sites(assembly, enzyme):
                     rigt_count += 1
         out.append('%s %d %d' % (key, left_count, rigt_count))
     return out
+
+
+def correct_links(gfa, hic_links):
+    """correct_links.cpp:70-354 as a second, independent restatement (the reference needs
+    boost::graph and cannot be compiled here: PARITY UNPINNED).  Dijkstra on unit weights is a
+    breadth-first search.  Emulated C++ behaviours: unordered_map::operator[] inserting id 0 for
+    unknown names, the vecS graph growing to the largest edge endpoint, (long)FLT_MAX failing the
+    INT_MIN/INT_MAX test, ostream's '%g' formatting of doubles, the inconsistent `added` keys.
+    Returns the stdout lines."""
+    from collections import deque
+
+    INT_MAX, INT_MIN, UNREACH = 2 ** 31 - 1, -2 ** 31, -2 ** 63
+
+    class IdMap(dict):
+        def __missing__(self, k):
+            self[k] = 0
+            return 0
+
+    unitig2id = IdMap()
+    out_edges = []
+    nid = 0
+
+    def add_edge(a, b):
+        while len(out_edges) <= max(a, b):
+            out_edges.append([])
+        out_edges[a].append(b)
+
+    with open(gfa, 'r', encoding='latin-1') as f:
+        for line in f:
+            line = line.rstrip('\n')
+            if not line:
+                continue
+            t = line.split()
+            if line[0] == 'S':
+                v = t[1] if len(t) > 1 else ''
+                for suf in (':FOW', ':REV'):
+                    if (v + suf) not in unitig2id:
+                        unitig2id[v + suf] = nid
+                        nid += 1
+            if line[0] == 'L':
+                t = t + [''] * 6
+                c1, o1, c2, o2 = t[1], t[2], t[3], t[4]
+                v1 = v2 = v3 = v4 = ''
+                if o1 == '+' and o2 == '+':
+                    v1, v2, v3, v4 = c1 + ':FOW', c2 + ':FOW', c2 + ':REV', c1 + ':REV'
+                if o1 == '+' and o2 == '-':
+                    v1, v2, v3, v4 = c1 + ':FOW', c2 + ':REV', c2 + ':FOW', c1 + ':REV'
+                if o1 == '-' and o2 == '+':
+                    v1, v2, v3, v4 = c1 + ':REV', c2 + ':FOW', c2 + ':REV', c1 + ':FOW'
+                if o1 == '-' and o2 == '-':
+                    v1, v2, v3, v4 = c1 + ':REV', c2 + ':REV', c2 + ':FOW', c1 + ':FOW'
+                a, b = unitig2id[v1], unitig2id[v2]
+                add_edge(a, b)
+                a, b = unitig2id[v3], unitig2id[v4]
+                add_edge(a, b)
+
+    def bfs(src):
+        d = [UNREACH] * len(out_edges)
+        if 0 <= src < len(out_edges):
+            d[src] = 0
+            q = deque([src])
+            while q:
+                x = q.popleft()
+                for y in out_edges[x]:
+                    if d[y] == UNREACH:
+                        d[y] = d[x] + 1
+                        q.append(y)
+        return d
+
+    def g6(x):
+        return '%g' % x
+
+    out = []
+    added = {}
+    with open(hic_links, 'r', encoding='latin-1') as f:
+        for line in f:
+            line = line.rstrip('\n')
+            t = line.split()
+            a = t[0] if len(t) > 0 else ''
+            b = t[1] if len(t) > 1 else ''
+            try:
+                c, d, e, ff = (float(t[i]) for i in (2, 3, 4, 5))
+            except (IndexError, ValueError):
+                c = d = e = ff = 0.0
+            x = t[6] if len(t) > 6 else ''
+            h = t[7] if len(t) > 7 else ''
+            if e < 1:
+                out.append(line)
+                continue
+            u, v = a[:-2] if len(a) >= 2 else '', b[:-2] if len(b) >= 2 else ''
+            if all((k not in unitig2id) for k in (u + ':FOW', u + ':REV', v + ':FOW', v + ':REV')):
+                out.append(line)
+                continue
+            dist_fow = bfs(unitig2id[u + ':FOW'])
+            dist_rev = bfs(unitig2id[u + ':REV'])
+            minpath, ori, ratio = -1, '', 0.1
+            done = printed = inlimits = False
+            for orientation in ('BB', 'BE', 'EB', 'EE'):
+                printed = False
+                v1 = u + (':REV' if orientation[0] == 'B' else ':FOW')
+                v2 = v + (':FOW' if orientation[1] == 'B' else ':REV')
+                if a not in added and b not in added:
+                    i1, i2 = unitig2id[v1], unitig2id[v2]
+                    if 0 <= i1 < len(out_edges) and i2 in out_edges[i1]:
+                        added[u] = True
+                        added[v] = True
+                        out.append('\t'.join([u + ':' + orientation[0], v + ':' + orientation[1], g6(c), g6(d), g6(e), g6(ff), x, h]))
+                        done = printed = True
+                        break
+                    dv = dist_rev if orientation[0] == 'B' else dist_fow
+                    path_len = dv[i2] if 0 <= i2 < len(dv) else UNREACH
+                    if INT_MIN < path_len < INT_MAX:
+                        inlimits = True
+                        if minpath == -1:
+                            minpath, ori = path_len, orientation
+                        elif path_len < minpath:
+                            ratio = 1.0 * path_len / minpath
+                            minpath, ori = path_len, orientation
+            if not inlimits:
+                continue
+            if 0 < ratio < 1 and INT_MIN < minpath < INT_MAX and not done:
+                out.append('\t'.join([u + ':' + ori[0], v + ':' + ori[1], g6(c), g6(d), g6(e), g6(ff), x, h]))
+                added[a] = True
+                printed = True
+                added[b] = True
+            elif not printed:
+                out.append(line)
+                added[a] = True
+                added[b] = True
+    return out

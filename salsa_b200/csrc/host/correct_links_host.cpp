@@ -1,0 +1,206 @@
+// correct_links_host.cpp -- drop-in for the reference's correct_links (correct_links.cpp:70-354):
+//
+//     correct_links -g GFA -l contig_links_scaled_sorted_iteration_1 > tmp.links
+//
+// Host program, no GPU work: the reference re-orients Hi-C links with the help of the assembly
+// graph -- a direct GFA edge between the two contig ends wins, otherwise the orientation with
+// the shortest graph path.  The reference needs boost::graph (not vendored, absent here, so it
+// cannot be compiled: parity is pinned only by oracle/py_twin.correct_links).  All GFA edges
+// have weight 1.0, so Dijkstra distances are breadth-first hop counts; they are computed once
+// per source vertex and cached instead of twice per link.
+//
+// Behaviours kept on purpose (they shape the output):
+//   * unordered_map::operator[] on unknown names yields vertex id 0 AND inserts the name
+//     (correct_links.cpp:172-173,216,224,265,283,289);
+//   * the graph has as many vertices as the largest edge endpoint + 1 (boost vecS add_edge);
+//     a vertex id beyond that is treated as unreachable here (the reference reads out of bounds);
+//   * unreachable = FLT_MAX -> `long` conversion fails the INT_MIN/INT_MAX test (:295): excluded;
+//   * `added` is keyed by bare contig names in the direct-edge case (:267-268) but looked up and
+//     otherwise written with the full "name:B|E" strings (:262,337,346-347);
+//   * a link whose ends were both "added" earlier, or with no finite path at all, prints nothing (:318-321);
+//   * numbers are re-printed with ostream's default 6 significant digits (:271,330).
+#include <getopt.h>
+
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+#include <queue>
+#include <sstream>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using std::string;
+
+namespace {
+
+struct Gfa {
+    std::unordered_map<string, int> id;          // "name:FOW" / "name:REV" -> vertex
+    std::vector<std::vector<int>> out;           // adjacency (directed)
+    std::unordered_map<int, std::vector<long>> dist_cache;
+
+    int vertex(const string &key) { return id[key]; }      // inserts 0 for unknown keys, like the reference
+
+    void add_edge(int a, int b)
+    {
+        size_t need = (size_t)std::max(a, b) + 1;
+        if (out.size() < need) out.resize(need);
+        out[a].push_back(b);
+    }
+
+    bool has_edge(int a, int b) const
+    {
+        if (a < 0 || (size_t)a >= out.size()) return false;
+        for (int x : out[a])
+            if (x == b) return true;
+        return false;
+    }
+
+    // hop counts from src; LONG_MIN stands for "unreachable" (what (long)FLT_MAX becomes on x86-64)
+    const std::vector<long> &distances(int src)
+    {
+        auto it = dist_cache.find(src);
+        if (it != dist_cache.end()) return it->second;
+        std::vector<long> d(out.size(), LONG_MIN);
+        if (src >= 0 && (size_t)src < out.size()) {
+            std::queue<int> q;
+            d[src] = 0;
+            q.push(src);
+            while (!q.empty()) {
+                int v = q.front();
+                q.pop();
+                for (int w : out[v])
+                    if (d[w] == LONG_MIN) { d[w] = d[v] + 1; q.push(w); }
+            }
+        }
+        return dist_cache.emplace(src, std::move(d)).first->second;
+    }
+};
+
+void load_gfa(const string &path, Gfa &g)
+{
+    std::ifstream in(path);
+    string line;
+    int next = 0;
+    while (std::getline(in, line)) {
+        if (line.empty()) continue;
+        std::istringstream iss(line);
+        string tag, a, b, c, d, e;
+        if (line[0] == 'S') {                                   // S name * LN:i:len   (:113-127)
+            iss >> tag >> a >> b >> c;
+            for (const char *suffix : {":FOW", ":REV"}) {
+                string key = a + suffix;
+                if (!g.id.count(key)) g.id[key] = next++;
+            }
+        }
+        if (line[0] == 'L') {                                   // L c1 +|- c2 +|- cigar   (:131-174)
+            iss >> tag >> a >> b >> c >> d >> e;
+            const string &c1 = a, &o1 = b, &c2 = c, &o2 = d;
+            string v1, v2, v3, v4;                              // stay empty for an unknown orientation pair
+            if (o1 == "+" && o2 == "+") { v1 = c1 + ":FOW"; v2 = c2 + ":FOW"; v3 = c2 + ":REV"; v4 = c1 + ":REV"; }
+            if (o1 == "+" && o2 == "-") { v1 = c1 + ":FOW"; v2 = c2 + ":REV"; v3 = c2 + ":FOW"; v4 = c1 + ":REV"; }
+            if (o1 == "-" && o2 == "+") { v1 = c1 + ":REV"; v2 = c2 + ":FOW"; v3 = c2 + ":REV"; v4 = c1 + ":FOW"; }
+            if (o1 == "-" && o2 == "-") { v1 = c1 + ":REV"; v2 = c2 + ":REV"; v3 = c2 + ":FOW"; v4 = c1 + ":FOW"; }
+            int i1 = g.vertex(v1), i2 = g.vertex(v2);
+            g.add_edge(i1, i2);
+            int i3 = g.vertex(v3), i4 = g.vertex(v4);
+            g.add_edge(i3, i4);
+        }
+    }
+}
+
+size_t edge_count(const Gfa &g)
+{
+    size_t n = 0;
+    for (auto &v : g.out) n += v.size();
+    return n;
+}
+
+}   // namespace
+
+int main(int argc, char **argv)
+{
+    string gfa, links;
+    int opt;
+    while ((opt = getopt(argc, argv, "g:l:")) != -1) {
+        if (opt == 'g') gfa = optarg;
+        else if (opt == 'l') links = optarg;
+        else { printf("Usage: misasm -g gfa -l hic_links\n"); return EXIT_FAILURE; }
+    }
+    if (gfa.empty() || links.empty()) { printf("Usage: misasm -g gfa -l hic_links\n"); return EXIT_FAILURE; }
+
+    Gfa g;
+    load_gfa(gfa, g);
+    std::cerr << "Done loading GFA file" << std::endl;
+    std::cerr << "Number of Nodes = " << g.out.size() << std::endl;
+    std::cerr << "Number of Edges = " << edge_count(g) << std::endl;
+
+    std::unordered_map<string, bool> added;
+    std::ifstream hic(links);
+    string line;
+    static const char *ORI[4] = {"BB", "BE", "EB", "EE"};
+    while (std::getline(hic, line)) {
+        string a, b, x, h;
+        double c = 0, d = 0, e = 0, f = 0;
+        std::istringstream iss(line);
+        iss >> a >> b >> c >> d >> e >> f >> x >> h;
+        if (e < 1) { std::cout << line << std::endl; continue; }                   // :196-200
+        string u = a.substr(0, a.length() >= 2 ? a.length() - 2 : 0);
+        string v = b.substr(0, b.length() >= 2 ? b.length() - 2 : 0);
+        if (!g.id.count(u + ":FOW") && !g.id.count(u + ":REV") && !g.id.count(v + ":FOW") && !g.id.count(v + ":REV")) {
+            std::cout << line << std::endl;                                        // :203-207
+            continue;
+        }
+        const std::vector<long> &from_fow = g.distances(g.vertex(u + ":FOW"));     // :216
+        const std::vector<long> dist_fow(from_fow);                                 // copy: the cache may rehash below
+        const std::vector<long> dist_rev(g.distances(g.vertex(u + ":REV")));       // :224
+
+        long minpath = -1;
+        string ori;
+        double ratio = 0.1;
+        bool done = false, printed = false, inlimits = false;
+        for (int k = 0; k < 4; k++) {
+            printed = false;
+            const bool from_rev = (k < 2);                       // BB, BE start from u:REV; EB, EE from u:FOW
+            string v1 = u + (from_rev ? ":REV" : ":FOW");
+            string v2 = v + ((k == 0 || k == 2) ? ":FOW" : ":REV");
+            if (added.count(a) || added.count(b)) continue;      // :262
+            int i1 = g.vertex(v1), i2 = g.vertex(v2);
+            if (g.has_edge(i1, i2)) {                            // :265-274
+                added[u] = true;
+                added[v] = true;
+                std::cout << u << ":" << ORI[k][0] << "\t" << v << ":" << ORI[k][1] << "\t" << c << "\t" << d << "\t" << e << "\t"
+                          << f << "\t" << x << "\t" << h << std::endl;
+                done = true;
+                printed = true;
+                break;
+            }
+            const std::vector<long> &dv = from_rev ? dist_rev : dist_fow;
+            long path_len = (i2 >= 0 && (size_t)i2 < dv.size()) ? dv[i2] : LONG_MIN;
+            if (path_len < INT_MAX && path_len > INT_MIN) {      // :295-316
+                inlimits = true;
+                if (minpath == -1) { minpath = path_len; ori = ORI[k]; }
+                else if (path_len < minpath) {
+                    ratio = 1.0 * path_len / minpath;
+                    minpath = path_len;
+                    ori = ORI[k];
+                }
+            }
+        }
+        if (!inlimits) continue;                                 // :318-321
+        if (ratio > 0 && ratio < 1 && minpath < INT_MAX && minpath > INT_MIN && !done) {     // :322-334
+            std::cout << u + ":" + ori[0] << '\t' << v + ":" + ori[1] << '\t' << c << "\t" << d << "\t" << e << "\t" << f << "\t" << x
+                      << "\t" << h << std::endl;
+            added[a] = true;
+            printed = true;
+            added[b] = true;
+        } else if (!printed) {                                   // :335-345
+            std::cout << line << std::endl;
+            added[a] = true;
+            added[b] = true;
+        }
+    }
+    return 0;
+}
