@@ -1,0 +1,80 @@
+"""Final scaffold FASTA + AGP writer: host-side consumer of scaffolds_iteration_N.p -- what
+get_seq.py does.  Scaffolds are numbered by decreasing length (get_seq.py:104-114), contigs are
+joined with 100-N gaps and `U 100 scaffold yes proximity_ligation` AGP lines (:160-170); the
+optional second AGP maps `_1`/`_2` pieces back to the pre-cleaning names and coordinates
+(:49-75,147-153)."""
+import pickle
+import re
+
+from .clean import read_fasta
+
+_COMP = {'A': 'T', 'B': 'N', 'C': 'G', 'G': 'C', 'T': 'A', 'N': 'N', 'R': 'N', 'M': 'N', 'Y': 'N', 'S': 'N', 'W': 'N', 'K': 'N',
+         'V': 'N', 'H': 'N', 'D': 'N', 'a': 't', 'c': 'g', 'g': 'c', 't': 'a', 'n': 'n', ' ': ''}
+
+
+def revcomp(s):
+    return ''.join(_COMP[b] for b in s)[::-1]      # KeyError on other characters, like the reference's table
+
+
+def original_coords(name, position, breaks):
+    if re.search(r"_[12]$", name) and name[:-2] in breaks:
+        orig = name[:-2]
+        return orig, position + (breaks[orig] if name.endswith('_2') else 0)
+    return name, position
+
+
+def write_outputs(cleaned, scaffold_map_path, fasta_out, agp_out, breaks_path=None, agp_orig_out=None):
+    if bool(breaks_path) ^ bool(agp_orig_out):
+        raise SystemExit("ERROR: Both -b, --breaks and -G, --agp-orig-coords must be supplied together. "
+                         "None or both are fine, but not one only.")
+    with open(scaffold_map_path, 'rb') as f:
+        scaff_map = pickle.load(f)
+    breaks = None
+    if breaks_path:
+        breaks = {}
+        with open(breaks_path, 'r') as fh:
+            for line in fh:
+                t = line.rstrip('\n').split('\t')
+                assert t[0] not in breaks
+                breaks[t[0]] = int(t[1])
+    seq = read_fasta(cleaned)
+    clen = {k: len(v) for k, v in seq.items()}
+    total = {s: sum(clen[p[i].split(':')[0]] for i in range(0, len(p) - 1, 2)) for s, p in scaff_map.items()}
+    ranked = sorted(total.items(), key=lambda kv: kv[1], reverse=True)        # stable: ties keep map order
+    orig = open(agp_orig_out, 'w') if agp_orig_out else None
+    with open(agp_out, 'w') as agp, open(fasta_out, 'w') as fa:
+        for cid, (key, _) in enumerate(ranked, 1):
+            path = scaff_map[key]
+            start, comp, parts = 1, 1, []
+            for i in range(0, len(path) - 1, 2):
+                cur, nxt = path[i].split(':'), path[i + 1].split(':')
+                n = clen[cur[0]]
+                end = n + start - 1
+                direction = ''
+                if cur[1] == 'B' and nxt[1] == 'E':
+                    parts.append(seq[cur[0]])
+                    direction = '+'
+                if cur[1] == 'E' and nxt[1] == 'B':
+                    parts.append(revcomp(seq[cur[0]]))
+                    direction = '-'
+                cols = ['scaffold_%d\t%d\t%d\t%d\tW' % (cid, start, end, comp), cur[0], '1', str(n), direction + '\n']
+                agp.write('\t'.join(cols))
+                if orig:
+                    oname, ostart = original_coords(cur[0], 1, breaks)
+                    cols[1], cols[2], cols[3] = oname, str(ostart), str(n + ostart - 1)
+                    orig.write('\t'.join(cols))
+                start, comp = end + 1, comp + 1
+                if i != len(path) - 2:
+                    parts.append('N' * 100)
+                    end = 100 + start - 1
+                    gap = 'scaffold_%d\t%d\t%d\t%d\tU\t100\tscaffold\tyes\tproximity_ligation\n' % (cid, start, end, comp)
+                    agp.write(gap)
+                    if orig:
+                        orig.write(gap)
+                    start, comp = end + 1, comp + 1
+            s = ''.join(parts)
+            fa.write('>scaffold_%d\n' % cid)
+            for i in range(0, len(s), 80):
+                fa.write(s[i:i + 80] + '\n')
+    if orig:
+        orig.close()
