@@ -34,7 +34,7 @@ namespace bedscan {
 #define SALSA_TILE 32768
 #endif
 #ifndef SALSA_MINBLOCKS
-#define SALSA_MINBLOCKS 4
+#define SALSA_MINBLOCKS 5
 #endif
 constexpr int TILE = SALSA_TILE;
 constexpr int HALO = SALSA_MAX_LINE;   // 1024
@@ -45,7 +45,7 @@ constexpr int WCAP = LCAP / NWARPS;    // per-warp segment
 constexpr int SUBTILE = 2048;          // fallback range: <= 2048 line starts by construction
 constexpr int SPARE_OFF = HALO + TILE + HALO + 32;      // one spare line (avoid mode: a line fetched from before the tile)
 constexpr int SMEM_BYTES = SPARE_OFF + HALO + 64;
-constexpr int SPWORDS = SMEM_BYTES / 32 + 4;   // special-byte bitmap, 1 bit per staged byte (+ guard words)
+constexpr int SPWORDS = SPARE_OFF / 32 + 8;   // special-byte bitmap, 1 bit per staged byte (+ guard words)
 constexpr int RW = 8;                  // read-name words carried per record (32 bytes)
 
 struct ScanArgs {
@@ -589,12 +589,9 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
             }
         }
         const int first_line_idx = (int)((long long)A.mis - sb);
-        Rec last;
-        last.id = -1; last.s_lo = last.s_hi = last.e_lo = last.e_hi = 0; last.name = last.read = 0; last.flags = 0;
-#pragma unroll
-        for (int j = 0; j < RW; j++) last.rw[j] = 0;
-        int last_start = -2;
-        for (int k0 = -1; k0 < cnt; k0 += 32) {
+        // steps overlap by one entry: lane 0 re-parses the previous step's last line and only plays
+        // "previous" (1/32 more parsing, but no record has to live across steps)
+        for (int k0 = -1; k0 + 1 < cnt; k0 += 31) {
             int k = k0 + lane;                       // entry -1 is the previous line, entries 0..cnt-1 are owned
             Rec rec;
             rec.id = -1; rec.s_lo = rec.s_hi = rec.e_lo = rec.e_hi = 0; rec.name = rec.read = 0; rec.flags = 0;
@@ -607,15 +604,12 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
             }
             Rec pv = rec_shfl_up(rec);
             int pstart = __shfl_up_sync(0xffffffffu, lstart, 1);
-            if (lane == 0) { pv = last; pstart = last_start; }
-            if (k >= 0 && k < cnt) {
+            if (lane >= 1 && k < cnt) {
                 nlines_acc++;
                 uint64_t off = A.base_offset + (uint64_t)((long long)lstart + sb - (long long)A.mis);
                 bool prev_is_first = sb <= 0 && pstart == first_line_idx;
                 if (Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
             }
-            last = rec_shfl_idx(rec, 31);
-            last_start = __shfl_sync(0xffffffffu, lstart, 31);
         }
         return;
     }
@@ -719,36 +713,44 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
 }
 
 constexpr size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
-constexpr size_t OFF_SP = align16(SMEM_BYTES);
-constexpr size_t OFF_SEG = OFF_SP + align16(SPWORDS * 4);
-constexpr size_t OFF_LINES = OFF_SEG + align16(LCAP * 2);
-constexpr size_t OFF_MASK = OFF_LINES + align16((LCAP + 8) * 2);
-constexpr size_t OFF_CARRY = OFF_MASK + align16(33 * RW * 4);
-constexpr size_t OFF_WCOUNT = OFF_CARRY + align16((NWARPS + 1) * sizeof(Rec));
-constexpr size_t OFF_IDV = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));       // avoid mode only from here
-constexpr size_t OFF_EXT = OFF_IDV + align16((LCAP + 8) * sizeof(int));
-constexpr size_t OFF_EXTINFO = OFF_EXT + align16(sizeof(Rec));
-constexpr size_t DYN_SMEM_PLAIN = OFF_IDV;
-constexpr size_t DYN_SMEM_AVOID = OFF_EXTINFO + 16;
+// Dynamic shared memory layout.  The plain kernels (warp-autonomous everywhere) need the staged
+// bytes, the special bitmap, the per-warp line-start segments and the byte-mask table: 44.4 KB, so
+// five CTAs fit one SM.  Avoid mode adds the spare line, the block-wide line list, the carry
+// records and the per-line contig ids.
+template <bool AV>
+struct Layout {
+    static constexpr size_t BYTES = AV ? (size_t)SMEM_BYTES : (size_t)SPARE_OFF;
+    static constexpr size_t OFF_SP = align16(BYTES);
+    static constexpr size_t OFF_SEG = OFF_SP + align16(SPWORDS * 4);
+    static constexpr size_t OFF_MASK = OFF_SEG + align16(LCAP * 2);
+    static constexpr size_t OFF_WCOUNT = OFF_MASK + align16(33 * RW * 4);
+    static constexpr size_t OFF_LINES = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));       // avoid mode only from here
+    static constexpr size_t OFF_CARRY = OFF_LINES + align16((LCAP + 8) * 2);
+    static constexpr size_t OFF_IDV = OFF_CARRY + align16((NWARPS + 1) * sizeof(Rec));
+    static constexpr size_t OFF_EXT = OFF_IDV + align16((LCAP + 8) * sizeof(int));
+    static constexpr size_t OFF_EXTINFO = OFF_EXT + align16(sizeof(Rec));
+    static constexpr size_t TOTAL = AV ? OFF_EXTINFO + 16 : OFF_LINES;
+};
 template <class Policy>
-constexpr size_t dyn_smem() { return Policy::AVOID ? DYN_SMEM_AVOID : DYN_SMEM_PLAIN; }
+constexpr size_t dyn_smem() { return Layout<Policy::AVOID>::TOTAL; }
 
 template <class Policy>
 __global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     Smem S;
+    typedef Layout<Policy::AVOID> LY;
     S.s = smem;
-    S.sp = reinterpret_cast<uint32_t *>(smem + OFF_SP);
-    S.seg = reinterpret_cast<uint16_t *>(smem + OFF_SEG);
-    S.lines = reinterpret_cast<uint16_t *>(smem + OFF_LINES);
-    S.lowmask = reinterpret_cast<uint32_t (*)[RW]>(smem + OFF_MASK);
-    S.carry = reinterpret_cast<Rec *>(smem + OFF_CARRY);
-    S.wcount = reinterpret_cast<int *>(smem + OFF_WCOUNT);
+    S.sp = reinterpret_cast<uint32_t *>(smem + LY::OFF_SP);
+    S.seg = reinterpret_cast<uint16_t *>(smem + LY::OFF_SEG);
+    S.lowmask = reinterpret_cast<uint32_t (*)[RW]>(smem + LY::OFF_MASK);
+    S.wcount = reinterpret_cast<int *>(smem + LY::OFF_WCOUNT);
     S.flagp = S.wcount + NWARPS;
-    S.idv = reinterpret_cast<int *>(smem + OFF_IDV);
-    S.ext = reinterpret_cast<Rec *>(smem + OFF_EXT);
-    S.extinfo = reinterpret_cast<int *>(smem + OFF_EXTINFO);
+    S.lines = reinterpret_cast<uint16_t *>(smem + LY::OFF_LINES);      // the rest exists in avoid mode only
+    S.carry = reinterpret_cast<Rec *>(smem + LY::OFF_CARRY);
+    S.idv = reinterpret_cast<int *>(smem + LY::OFF_IDV);
+    S.ext = reinterpret_cast<Rec *>(smem + LY::OFF_EXT);
+    S.extinfo = reinterpret_cast<int *>(smem + LY::OFF_EXTINFO);
     uint8_t *s = S.s;
     __shared__ __align__(8) uint64_t bar;
 
@@ -838,7 +840,7 @@ __global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typ
             if (tid == 0) *S.flagp = 0;
             __syncthreads();
             long long h2 = lo + SUBTILE < hi ? lo + SUBTILE : hi;
-            process_range<Policy, false, false>(PA, A, S, sb, lo, h2, l0, sent, trunc, nlines, npairs);
+            process_range<Policy, false, !Policy::AVOID>(PA, A, S, sb, lo, h2, l0, sent, trunc, nlines, npairs);
         }
     }
     // ---- statistics: one atomic pair per CTA -----------------------------
