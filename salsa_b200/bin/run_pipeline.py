@@ -68,10 +68,17 @@ def main(argv=None):
     os.makedirs(out, exist_ok=True)
     log = open(out + '/commands.log', 'w', 1)
 
+    import time
+    timings = open(out + '/timings.tsv', 'a', 1)      # extra to the reference: wall seconds per step
+
     def sh(cmd, fatal=True, cleanup=None):
         print(cmd)
         log.write(cmd + '\n')
+        t0 = time.time()
         r = subprocess.run(cmd, shell=True, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        words = cmd.split()
+        step = os.path.basename(words[1] if words[0] == py else words[0])
+        timings.write('%s\t%.3f\n' % (step, time.time() - t0))
         if r.returncode != 0:
             print(r.stdout + r.stderr, file=sys.stderr)
             if cleanup and os.path.isfile(cleanup):

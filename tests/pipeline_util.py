@@ -92,7 +92,7 @@ def comparable(outdir):
     res = {}
     for fn in sorted(os.listdir(outdir)):
         p = os.path.join(outdir, fn)
-        if os.path.islink(p) or not os.path.isfile(p) or fn.endswith('.p') or fn in ('commands.log',) or fn.endswith('.log'):
+        if os.path.islink(p) or not os.path.isfile(p) or fn.endswith('.p') or fn in ('commands.log', 'timings.tsv') or fn.endswith('.log'):
             continue
         data = open(p, 'rb').read()
         if fn.startswith(('misasm_iteration_', 'input_breaks', 're_counts_iteration_1')):

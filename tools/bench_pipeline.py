@@ -1,0 +1,63 @@
+#!/usr/bin/env python
+"""Wall seconds per pipeline iteration (the second half of BASELINE.json's metric) on
+BASELINE configs[0]: synthetic 2 Mb genome in 200 contigs, 1 M Hi-C pairs, -e GATC -i 3.
+
+Runs the drop-in run_pipeline.py twice over the same inputs: with the CUDA step programs
+(salsa_b200/bin) and with the CPU steps (oracle C port + compiled reference coverage tools; the
+reference's own Python-2 steps cannot run in this image).  The host-side steps (layout,
+re-projection, AGP) are the same code in both runs.  Prints one JSON line.
+"""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tests'))
+
+import pipeline_util as pu  # noqa: E402
+
+
+def run(bin_dir, data, out, extra):
+    cmd = [sys.executable, os.path.join(pu.BIN, 'run_pipeline.py'), '--bin', bin_dir, '-a', data + '/assembly.fa', '-l',
+           data + '/contigs.len', '-b', data + '/reads.bed', '-o', out] + extra
+    t0 = time.time()
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    wall = time.time() - t0
+    steps = {}
+    for ln in open(out + '/timings.tsv'):
+        k, v = ln.split('\t')
+        steps[k] = steps.get(k, 0.0) + float(v)
+    iters = len([f for f in os.listdir(out) if f.startswith('contig_links_iteration_')])
+    return wall, steps, iters
+
+
+def main():
+    pairs = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+    d = tempfile.mkdtemp()
+    data = d + '/data'
+    pu.write_dataset(data, ncontig=200, genome=2_000_000, len_lo=2_000, len_hi=40_000, npairs=pairs, seed=20261107, nchrom=4)
+    import oracle
+    oracle.build()
+    obin = pu.make_oracle_bin(d + '/obin')
+    args = ['-e', 'GATC', '-i', '3', '-m', 'no']
+    wg, sg, ig = run(pu.BIN, data, d + '/gpu', args)
+    wo, so, io = run(obin, data, d + '/cpu', args)
+    same = open(d + '/gpu/scaffolds_FINAL.agp').read() == open(d + '/cpu/scaffolds_FINAL.agp').read()
+    hot = ('make_links.py', 'fast_scaled_scores.py', 'RE_sites.py', 'break_contigs', 'break_contigs_start')
+    print(json.dumps({
+        'metric': 'seconds_per_pipeline_iteration', 'config': 'BASELINE configs[0]: 2 Mb genome, 200 contigs, %d pairs, -e GATC -i 3 -m no' % pairs,
+        'iterations_run': ig, 'identical_final_agp': same,
+        'gpu_path': {'wall_s': wg, 's_per_iteration': wg / ig, 'hot_steps_s': sum(sg.get(k, 0) for k in hot), 'steps_s': sg},
+        'cpu_path': {'wall_s': wo, 's_per_iteration': wo / io, 'hot_steps_s': sum(so.get(k, 0) for k in hot), 'steps_s': so,
+                     'kind': 'oracle C port + compiled reference break_contigs*, 1 core'},
+        'note': 'each GPU step is a fresh process (python + torch import + CUDA context, ~3-5 s) exactly like the reference spawns '
+                'its steps; at this tiny size that start-up dominates the GPU path.  Host-side Python steps are shared.'}))
+
+
+if __name__ == '__main__':
+    main()
