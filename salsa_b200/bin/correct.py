@@ -6,5 +6,13 @@ import sys
 import _common  # noqa: F401
 from salsa_b200.host import clean
 
+
+
+def main(argv=None):
+    a = sys.argv[1:] if argv is None else argv
+    clean.clean(a[0], a[1], a[2], a[3])
+    return 0
+
+
 if __name__ == '__main__':
-    clean.clean(sys.argv[1], sys.argv[2], sys.argv[3], sys.argv[4])
+    sys.exit(main())

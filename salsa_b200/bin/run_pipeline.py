@@ -57,6 +57,7 @@ def main(argv=None):
     ap.add_argument('-f', '--filter', default='no', help='Filter bed file for contigs present in the assembly')
     ap.add_argument('-p', '--prnt', default='no', help='"yes" to output scaffolds and agp for each iteration')
     ap.add_argument('--bin', default=here, help=argparse.SUPPRESS)      # where the step programs live
+    ap.add_argument('--subprocess', action='store_true', help=argparse.SUPPRESS)   # spawn every step like the reference
     args = ap.parse_args(argv)
     if args.orig_coords and args.clean != 'yes':
         print("ERROR: You must use -m,--clean 'yes' with -O,--output-original-coords.", file=sys.stderr)
@@ -71,21 +72,63 @@ def main(argv=None):
     import time
     timings = open(out + '/timings.tsv', 'a', 1)      # extra to the reference: wall seconds per step
 
+    # The Python steps of THIS package run inside this process by default: one interpreter, one CUDA
+    # context and one loaded library for the whole run instead of ~4 s of start-up per step.  The
+    # command lines are still logged as the reference would run them; --subprocess restores spawning.
+    inproc = (os.path.abspath(B) == here) and not args.subprocess
+    modules = {}
+
+    def run_inprocess(words, redirect):
+        import contextlib
+        import importlib.util
+        import io
+        path = words[1]
+        name = os.path.basename(path)
+        if name not in modules:
+            if here not in sys.path:
+                sys.path.insert(0, here)
+            spec = importlib.util.spec_from_file_location('salsa_step_' + name[:-3], path)
+            modules[name] = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(modules[name])
+        buf = io.StringIO()
+        try:
+            with contextlib.redirect_stdout(buf):
+                rc = modules[name].main(words[2:]) or 0
+        except SystemExit as e:
+            rc = e.code if isinstance(e.code, int) else (0 if e.code is None else 1)
+        except Exception as e:                       # what would be a non-zero exit of the step program
+            print('%s: %s: %s' % (name, type(e).__name__, e), file=sys.stderr)
+            rc = 1
+        if redirect and rc == 0:
+            with open(redirect, 'w') as f:
+                f.write(buf.getvalue())
+        elif redirect:
+            open(redirect, 'w').close()
+        return rc
+
     def sh(cmd, fatal=True, cleanup=None):
         print(cmd)
         log.write(cmd + '\n')
         t0 = time.time()
-        r = subprocess.run(cmd, shell=True, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
         words = cmd.split()
         step = os.path.basename(words[1] if words[0] == py else words[0])
+        if inproc and words[0] == py and step.endswith('.py'):
+            redirect = None
+            if '>' in words:
+                redirect = words[words.index('>') + 1]
+                words = words[:words.index('>')]
+            rc, errtext = run_inprocess(words, redirect), ''
+        else:
+            r = subprocess.run(cmd, shell=True, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+            rc, errtext = r.returncode, r.stdout + r.stderr
         timings.write('%s\t%.3f\n' % (step, time.time() - t0))
-        if r.returncode != 0:
-            print(r.stdout + r.stderr, file=sys.stderr)
+        if rc != 0:
+            print(errtext, file=sys.stderr)
             if cleanup and os.path.isfile(cleanup):
                 os.remove(cleanup)
             if fatal:
                 sys.exit(1)
-        return r.returncode == 0
+        return rc == 0
 
     def get_seq(pickle_iter, tag):
         cmd = '%s %s/get_seq.py -a %s/assembly.cleaned.fasta -f %s/scaffolds_%s.fasta -g %s/scaffolds_%s.agp -p %s/scaffolds_iteration_%s.p' % (
@@ -166,8 +209,7 @@ def main(argv=None):
     it = 2
     ng50.append(ng50_of(lengths_of(it), genome_size))
     if it - 1 == int(args.iter):
-        os.system(get_seq(args.iter, 'FINAL'))
-        log.write(get_seq(args.iter, 'FINAL') + '\n')
+        sh(get_seq(args.iter, 'FINAL'), fatal=False)
         return 0
     # ---- iterations >= 2 (run_pipeline.py:271-385)
     while True:
@@ -179,12 +221,10 @@ def main(argv=None):
         misjoin_steps(it, False)
         ng50.append(ng50_of(lengths_of(it + 1), genome_size))
         if ng50[-1] == ng50[-2]:
-            log.write(get_seq(it - 1, 'FINAL') + '\n')
-            os.system(get_seq(it - 1, 'FINAL'))
+            sh(get_seq(it - 1, 'FINAL'), fatal=False)
             return 0
         if it - 1 == int(args.iter):
-            log.write(get_seq(args.iter, 'FINAL') + '\n')
-            os.system(get_seq(args.iter, 'FINAL'))
+            sh(get_seq(args.iter, 'FINAL'), fatal=False)
             return 0
         it += 1
 
