@@ -392,6 +392,36 @@ int salsa_cov_analyse(const int32_t *d_diff, int32_t *d_cov, const salsa_cov_seg
                       void *stream);
 
 /*
+ * Re-projection of the iteration-1 BED into scaffold coordinates: the BED
+ * pass of update_bed, layout_unitigs.py:816-886 (refactor = 0) and
+ * refactor_breaks.py:133-203 (refactor = 1).  The whole BED is resident at
+ * d_bed; contigs are those of salsa_names_build; per contig id:
+ * d_scaffold_of (scaffold index, -1 = in no scaffold), d_offset (start of
+ * the contig inside its scaffold), d_length, d_reversed (path orientation
+ * E..B).  Scaffold names: concatenated bytes + d_scaf_name_off[nscaf + 1].
+ *  1. salsa_reproject_candidates: one scan of the BED; appends (unordered)
+ *     the file offset of every line that closes a kept pair (refactor = 0)
+ *     or opens a same-contig run (refactor = 1) to d_cand; *d_count gets the
+ *     number found, which may exceed `capacity` -- then grow and repeat.
+ *     Data errors (missing fields or '/', bad integers) land in d_stats as
+ *     for the ingest; the reference raises IndexError / ValueError there.
+ *  2. salsa_sort_u64 (CUB) puts them in file order = output order.
+ *  3. salsa_reproject_emit with d_out == NULL writes each candidate's output
+ *     byte count to d_out_off[k]; after salsa_exclusive_scan_u64 over
+ *     ncand + 1 entries (last = 0 -> total) the same call with d_out writes
+ *     "scaffold\tstart\tend\tread\n" twice per kept pair (:864-871).
+ */
+int salsa_reproject_candidates(salsa_ctx *ctx, const void *d_bed, size_t nbytes, int32_t refactor,
+                               const int32_t *d_scaffold_of, uint64_t *d_cand, size_t capacity,
+                               uint64_t *d_count, uint64_t *d_stats, void *stream);
+int salsa_sort_u64(uint64_t *d_in, uint64_t *d_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream);
+int salsa_reproject_emit(salsa_ctx *ctx, const void *d_bed, size_t nbytes, int32_t refactor,
+                         const uint64_t *d_cand, size_t ncand, const int32_t *d_scaffold_of,
+                         const int64_t *d_offset, const int64_t *d_length, const uint8_t *d_reversed,
+                         const char *d_scaf_names, const uint32_t *d_scaf_name_off, uint64_t *d_out_off,
+                         void *d_out, size_t out_capacity, uint64_t *d_stats, void *stream);
+
+/*
  * Host-side text assembly (no float conversion happens here: text is built
  * from the integer digits the device produced).
  * salsa_format_g12   : str(float) strings, concatenated; h_off[n+1] offsets

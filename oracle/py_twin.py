@@ -1,4 +1,5 @@
-"""py_twin.py -- line-by-line Python-3 twin of the reference's three Python-2 scripts.
+"""py_twin.py -- line-by-line Python-3 twin of the reference's Python-2 hot-path scripts
+(make_links, fast_scaled_scores, RE_sites, correct_links, the BED pass of update_bed).
 
 TEST INFRASTRUCTURE ONLY (see oracle/salsa_oracle.c header): an independent
 second restatement used to cross-check the C oracle on small inputs.  Pure
@@ -363,3 +364,37 @@ def correct_links(gfa, hic_links):
                 added[a] = True
                 added[b] = True
     return out
+
+
+def reproject_bed(src, dst, c2s, info, contig_length, refactor):
+    """The BED pass of update_bed: layout_unitigs.py:816-886 (refactor=False) and
+    refactor_breaks.py:133-203 (refactor=True).  Sliding adjacent-line window over the
+    iteration-1 BED; byte strings, so ``split()`` has the Python-2 whitespace set.
+    c2s: contig -> scaffold key; info: contig -> (offset, end, 'FOW'|'REV'); str keys."""
+    def mapped(attrs, contig):
+        off, _, ori = info[contig]
+        s, e = int(attrs[1]), int(attrs[2])
+        if ori == 'FOW':
+            return off + s, off + e
+        return off + contig_length[contig] - e, off + contig_length[contig] - s
+
+    with open(src, 'rb') as f, open(dst, 'wb') as out:
+        prev_line = b''
+        for line in f:
+            if prev_line == b'':
+                prev_line = line
+                continue
+            pa, ca = prev_line.split(), line.split()
+            pc, cc = pa[0].decode('latin-1'), ca[0].decode('latin-1')
+            if refactor and pc == cc:
+                continue                                    # prev_line stays (refactor_breaks.py:150-151)
+            pr, cr = pa[3].split(b'/'), ca[3].split(b'/')
+            first, second = pr[1], cr[1]                    # IndexError without '/', like the reference
+            if pc in c2s and cc in c2s:
+                ps, cs = c2s[pc], c2s[cc]
+                if pr[0] == cr[0] and first == b'1' and second == b'2' and (not refactor or ps != cs):
+                    a, b = mapped(pa, pc)
+                    out.write(b'%s\t%d\t%d\t%s\n' % (ps.encode('latin-1'), a, b, pa[3]))
+                    a, b = mapped(ca, cc)
+                    out.write(b'%s\t%d\t%d\t%s\n' % (cs.encode('latin-1'), a, b, ca[3]))
+            prev_line = line

@@ -16,3 +16,9 @@ def engine():
         from salsa_b200.engine import Engine
         _ENGINE = Engine(int(os.environ.get('SALSA_B200_DEVICE', '0')))
     return _ENGINE
+
+
+def bed_pass():
+    """The CUDA BED pass for salsa_b200.host.reproject.update_bed (no CPU alternative here)."""
+    from salsa_b200 import reproject
+    return reproject.bed_pass(engine())

@@ -3,8 +3,8 @@
 
     layout_unitigs.py -x GFA|abc -l SORTED_LINKS -c CUTOFF -i N -d DIR
 
-Host-side step (the greedy layout stays on the host and consumes the byte-identical sorted
-links the GPU path produces).  Writes scaffolds_iteration_N.p, breakpoints_iteration_{N+1}.txt,
+The greedy layout stays on the host (it consumes the byte-identical sorted links the GPU path
+produces); the re-projection of the iteration-1 BED that follows it runs on the GPU.  Writes scaffolds_iteration_N.p, breakpoints_iteration_{N+1}.txt,
 alignment_iteration_{N+1}.bed, scaffold_length_iteration_{N+1}, re_counts_iteration_{N+1}.
 `-x`, `-u`, `-t` are accepted and ignored: the reference never loads them on this code path
 (layout_unitigs.py:98,206-211)."""
@@ -16,7 +16,7 @@ import _common  # noqa: F401  (puts the repository root on sys.path)
 from salsa_b200.host import reproject, scaffold_graph
 
 
-def main(argv=None):
+def main(argv=None, bed_pass=None):
     ap = argparse.ArgumentParser()
     ap.add_argument('-x', '--graph', default='abc')
     ap.add_argument('-l', '--links', required=True)
@@ -37,7 +37,7 @@ def main(argv=None):
     expanded, contig_length = scaffold_graph.layout(a.directory, it, int(a.cutoff), previous)
     with open('%s/scaffolds_iteration_%d.p' % (a.directory, it), 'wb') as f:
         pickle.dump(expanded, f)
-    reproject.update_bed(a.directory, expanded, contig_length, it + 1, refactor=False)
+    reproject.update_bed(a.directory, expanded, contig_length, it + 1, refactor=False, bed_pass=bed_pass or _common.bed_pass())
     return 0
 
 

@@ -66,7 +66,12 @@ def main(argv=None):
     eng.set_contigs(nm, lens, rl, rr, has_re, avoid)
     eng.begin_links('auto')
     print('bedfile started', file=sys.stderr)
-    eng.ingest_file(args.mapping)
+    from salsa_b200.reproject import resident_bed
+    bed = resident_bed(args.mapping, eng.device, load=False)      # left in HBM by the re-projection that wrote it
+    if bed is not None:
+        eng.ingest_device(bed)
+    else:
+        eng.ingest_file(args.mapping)
     eng.stats_read()                      # raises DataError where the reference would raise
     print('bedfile loaded', file=sys.stderr)
     sc = eng.score_links()

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Drop-in for the reference's refactor_breaks.py:   refactor_breaks.py -d DIR -i N
-Host-side step: splits scaffolds at the joins misasm_iteration_N.report flags, writes
-links_avoid_iteration_N, rewrites scaffolds_iteration_{N-1}.p and re-projects the BED."""
+Splits scaffolds at the joins misasm_iteration_N.report flags, writes links_avoid_iteration_N and
+rewrites scaffolds_iteration_{N-1}.p on the host; re-projects the BED on the GPU."""
 import argparse
 import sys
 
@@ -9,12 +9,12 @@ import _common  # noqa: F401
 from salsa_b200.host import breaks
 
 
-def main(argv=None):
+def main(argv=None, bed_pass=None):
     ap = argparse.ArgumentParser()
     ap.add_argument('-i', '--iteration')
     ap.add_argument('-d', '--directory')
     a = ap.parse_args(argv)
-    breaks.refactor(a.directory, int(a.iteration))
+    breaks.refactor(a.directory, int(a.iteration), bed_pass or _common.bed_pass())
     return 0
 
 

@@ -63,7 +63,7 @@ struct Rec {
     int e_lo, e_hi;       // end (int64)
     uint32_t name;        // noff | nlen << 16   (smem offsets)
     uint32_t read;        // roff | rcmp << 16: rcmp = number of read-name bytes the policy compares
-    uint32_t flags;       // nf (bits 0-2) | numbad (bit 3) | toolong (bit 4)
+    uint32_t flags;       // nf (bits 0-2) | numbad (bit 3) | toolong (bit 4) | whole read token length << 8 (NEED_RFULL policies)
     uint32_t rw[RW];      // first min(rcmp, 32) read-name bytes, zero padded
 };
 
@@ -411,6 +411,7 @@ __device__ __forceinline__ Rec parse_any(const ScanArgs &A, const Smem &S, int l
         int rcmp = Policy::read_cmp_len(rslash, rfull);
         int roff = (int)(rec.read & 0xFFFF);
         rec.read = (uint32_t)roff | ((uint32_t)rcmp << 16);
+        if (Policy::NEED_RFULL) rec.flags |= (uint32_t)rfull << 8;
         pack_read(S, roff, rcmp, rec.rw);
     }
     return rec;

@@ -1,7 +1,8 @@
 """Contig -> scaffold re-projection of the iteration-1 BED, scaffold lengths and per-scaffold
 RE counts: what layout_unitigs.py:708-886 (after every layout) and refactor_breaks.py:35-203
-(after every misjoin check) do with their `update_bed`.  Host-side; SURVEY section 8(f) ranks a
-GPU version of the BED pass as the next widening of the hot path.
+(after every misjoin check) do with their `update_bed`.  The placement tables, scaffold lengths
+and RE proration are host-side; the pass over the BED itself is injected (`bed_pass`): the product
+uses the CUDA one (salsa_b200/reproject.py, csrc/reproject.cu), the tests' CPU runs the oracle's.
 
 Differences between the two reference variants, both kept:
   * layout variant  : writes alignment_iteration_{N+1}.bed only if it does not exist yet
@@ -60,45 +61,10 @@ def scaffold_re_counts(scaffolds, info, slen, contig_length, re_counts):
     return out
 
 
-def _map(line_attrs, contig, info, contig_length):
-    off, _, ori = info[contig]
-    s, e = int(line_attrs[1]), int(line_attrs[2])
-    if ori == 'FOW':
-        return off + s, off + e
-    return off + contig_length[contig] - e, off + contig_length[contig] - s
-
-
-def reproject_bed(src, dst, c2s, info, contig_length, refactor):
-    """The BED pass of update_bed.  Sliding adjacent-line window over the iteration-1 BED."""
-    with open(src, 'r', encoding='latin-1', newline='\n') as f, open(dst, 'w', encoding='latin-1', newline='\n') as out:
-        prev_line = ''
-        buf = []
-        for line in f:
-            if prev_line == '':
-                prev_line = line
-                continue
-            pa, ca = prev_line.split(), line.split()
-            pc, cc = pa[0], ca[0]
-            if refactor and pc == cc:
-                continue                                    # prev_line stays (refactor_breaks.py:150-151)
-            pr, cr = pa[3].split('/'), ca[3].split('/')
-            first, second = pr[1], cr[1]                    # IndexError without '/', like the reference
-            if pc in c2s and cc in c2s:
-                ps, cs = c2s[pc], c2s[cc]
-                if pr[0] == cr[0] and first == '1' and second == '2' and (not refactor or ps != cs):
-                    a, b = _map(pa, pc, info, contig_length)
-                    buf.append('%s\t%d\t%d\t%s\n' % (ps, a, b, pa[3]))
-                    a, b = _map(ca, cc, info, contig_length)
-                    buf.append('%s\t%d\t%d\t%s\n' % (cs, a, b, ca[3]))
-                    if len(buf) >= 1000000:
-                        out.writelines(buf)
-                        buf = []
-            prev_line = line
-        out.writelines(buf)
-
-
-def update_bed(directory, scaffolds, contig_length, out_iteration, refactor):
-    """Writes alignment_iteration_{out}.bed, scaffold_length_iteration_{out}, re_counts_iteration_{out}."""
+def update_bed(directory, scaffolds, contig_length, out_iteration, refactor, bed_pass):
+    """Writes alignment_iteration_{out}.bed, scaffold_length_iteration_{out}, re_counts_iteration_{out}.
+    bed_pass(src, dst, c2s, info, contig_length, refactor) does the BED pass itself: the step
+    scripts pass the GPU one (salsa_b200.reproject.bed_pass)."""
     re_counts = {}
     with open(directory + '/re_counts_iteration_1', 'r', encoding='latin-1') as f:
         for line in f:
@@ -108,7 +74,7 @@ def update_bed(directory, scaffolds, contig_length, out_iteration, refactor):
     sre = scaffold_re_counts(scaffolds, info, slen, contig_length, re_counts)
     dst = '%s/alignment_iteration_%d.bed' % (directory, out_iteration)
     if refactor or not os.path.isfile(dst):
-        reproject_bed(directory + '/alignment_iteration_1.bed', dst, c2s, info, contig_length, refactor)
+        bed_pass(directory + '/alignment_iteration_1.bed', dst, c2s, info, contig_length, refactor)
     with open('%s/scaffold_length_iteration_%d' % (directory, out_iteration), 'w') as f:
         for key in slen:
             f.write('%s\t%d\n' % (key, slen[key]))

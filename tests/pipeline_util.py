@@ -1,8 +1,9 @@
 """Helpers for the end-to-end pipeline tests: a synthetic data set on disk, and an
 "oracle bin" directory whose accelerated steps (make_links.py, fast_scaled_scores.py,
-RE_sites.py, break_contigs, break_contigs_start) are the CPU oracle / the compiled reference,
-while the host-side steps are the product's own -- so a run with it and a run with
-salsa_b200/bin differ ONLY in the hot-path implementation."""
+RE_sites.py, break_contigs, break_contigs_start, the BED pass inside layout_unitigs.py and
+refactor_breaks.py) are the CPU oracle / the compiled reference, while the host-side steps are
+the product's own -- so a run with it and a run with salsa_b200/bin differ ONLY in the hot-path
+implementation."""
 import os
 import stat
 import sys
@@ -47,6 +48,26 @@ sys.stdout.write(''.join('%s %d %d\\n' % (n.decode('latin-1'), l, r) for n, l, r
 ''',
 }
 
+# the product's host-side step with the oracle's BED pass injected in place of the CUDA one
+HOST_STEP = '''#!%(py)s
+import sys
+sys.path.insert(0, %(root)r)
+sys.path.insert(0, %(bin)r)
+import importlib.util
+from oracle import py_twin
+spec = importlib.util.spec_from_file_location('product_step', %(bin)r + '/%(name)s')
+mod = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(mod)
+
+
+def main(argv=None):
+    return mod.main(argv, bed_pass=py_twin.reproject_bed)
+
+
+if __name__ == '__main__':
+    sys.exit(main())
+'''
+
 
 def make_oracle_bin(dst):
     os.makedirs(dst, exist_ok=True)
@@ -58,7 +79,12 @@ def make_oracle_bin(dst):
         p = os.path.join(dst, prog)
         open(p, 'w').write('#!/bin/sh\nexec %s/%s "$@"\n' % (ref, prog))
         os.chmod(p, os.stat(p).st_mode | stat.S_IXUSR | stat.S_IXGRP | stat.S_IXOTH)
-    for name in ('layout_unitigs.py', 'refactor_breaks.py', 'correct.py', 'get_seq.py', '_common.py', 'correct_links'):
+    for name in ('layout_unitigs.py', 'refactor_breaks.py'):
+        p = os.path.join(dst, name)
+        if os.path.lexists(p):
+            os.remove(p)
+        open(p, 'w').write(HOST_STEP % dict(py=sys.executable, root=ROOT, bin=BIN, name=name))
+    for name in ('correct.py', 'get_seq.py', '_common.py', 'correct_links'):
         d = os.path.join(dst, name)
         if os.path.lexists(d):
             os.remove(d)

@@ -1,0 +1,167 @@
+"""GPU parity tests of the BED re-projection (update_bed's pass over alignment_iteration_1.bed,
+layout_unitigs.py:816-886 and refactor_breaks.py:133-203) against the oracle's twin: the output
+file must be byte-identical, in both variants."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, 'salsa_b200', 'bin')
+
+
+@pytest.fixture(scope='module')
+def eng():
+    sys.path.insert(0, BIN)
+    from _common import engine
+    return engine()
+
+
+def placement(rng, names, lengths, nscaf, unplaced=0.2):
+    """Random scaffolds over the contigs -> (c2s, info) as salsa_b200.host.reproject.placement builds them."""
+    c2s, info = {}, {}
+    offs = [0] * nscaf
+    for nm, ln in zip(names, lengths):
+        if rng.random() < unplaced:
+            continue
+        k = int(rng.integers(nscaf))
+        key = 'scaffold_%d' % (k + 1)
+        c2s[nm] = key
+        info[nm] = (offs[k], offs[k] + ln, 'FOW' if rng.random() < 0.5 else 'REV')
+        offs[k] += ln
+    return c2s, info
+
+
+def both(eng, tmp_path, bed, names, lengths, c2s, info, refactor):
+    from oracle import py_twin
+    from salsa_b200 import reproject
+    src = str(tmp_path / 'src.bed')
+    open(src, 'wb').write(bed)
+    clen = dict(zip(names, lengths))
+    py_twin.reproject_bed(src, str(tmp_path / 'want.bed'), c2s, info, clen, refactor)
+    reproject.bed_pass(eng)(src, str(tmp_path / 'got.bed'), c2s, info, clen, refactor)
+    return open(str(tmp_path / 'got.bed'), 'rb').read(), open(str(tmp_path / 'want.bed'), 'rb').read()
+
+
+def random_bed(rng, names, lengths, npairs, same=0.15, noise=0.1):
+    out = []
+    n = len(names)
+    for r in range(npairs):
+        a = int(rng.integers(n))
+        b = a if rng.random() < same else int(rng.integers(n))
+        rows = [(a, '1'), (b, '2')]
+        u = rng.random()
+        if u < noise / 4:
+            rows = rows[:1]                              # orphan mate
+        elif u < noise / 2:
+            rows = [(a, '2'), (b, '1')]                  # wrong mate order
+        elif u < 3 * noise / 4:
+            rows.append((int(rng.integers(n)), '2'))     # supplementary third line
+        elif u < noise:
+            rows = [(a, '1/x'), (b, '2/y')]              # more than one '/'
+        for c, mate in rows:
+            s = int(rng.integers(0, max(1, lengths[c] - 50)))
+            sep = '\t' if rng.random() < 0.9 else '  '
+            tail = '\t37\t+' if rng.random() < 0.5 else ''
+            out.append('%s%s%d%s%d%sread%d/%s%s' % (names[c], sep, s, sep, s + 50, sep, r, mate, tail))
+    return ('\n'.join(out) + '\n').encode('latin-1')
+
+
+@pytest.mark.parametrize('refactor', [False, True])
+@pytest.mark.parametrize('seed,ncontig,npairs', [(1, 5, 200), (2, 40, 5000), (3, 300, 60000)])
+def test_random(eng, tmp_path, refactor, seed, ncontig, npairs):
+    rng = np.random.default_rng(seed)
+    names = ['ctg%d' % i if i % 7 else 'a_rather_long_contig_name_%d' % i for i in range(ncontig)]
+    lengths = [int(x) for x in rng.integers(100, 100000, ncontig)]
+    c2s, info = placement(rng, names, lengths, max(2, ncontig // 4))
+    bed = random_bed(rng, names + ['not_in_the_assembly'], lengths + [5000], npairs)
+    got, want = both(eng, tmp_path, bed, names, lengths, c2s, info, refactor)
+    assert len(want) > 0
+    assert got == want
+
+
+@pytest.mark.parametrize('refactor', [False, True])
+def test_known_answers(eng, tmp_path, refactor):
+    names, lengths = ['A', 'B', 'C'], [100, 200, 300]
+    c2s = {'A': 'scaffold_1', 'B': 'scaffold_1', 'C': 'scaffold_2'}
+    info = {'A': (0, 100, 'FOW'), 'B': (100, 300, 'REV'), 'C': (0, 300, 'FOW')}
+    bed = (b'A\t10\t20\tr1/1\n' b'C\t30\t40\tr1/2\n'         # kept by both: different scaffolds
+           b'A\t1\t2\tr2/1\n' b'B\t50\t60\tr2/2\n'           # same scaffold: layout keeps, refactor drops
+           b'B\t5\t6\tr3/1\n' b'B\t7\t8\tr3/2\n'             # same contig
+           b'C\t9\t19\tr4/1\n' b'A\t3\t4\tr4/2')             # no final newline
+    got, want = both(eng, tmp_path, bed, names, lengths, c2s, info, refactor)
+    assert got == want
+    if not refactor:
+        assert got.startswith(b'scaffold_1\t10\t20\tr1/1\nscaffold_2\t30\t40\tr1/2\n'
+                              b'scaffold_1\t1\t2\tr2/1\nscaffold_1\t240\t250\tr2/2\n')
+    else:
+        # r2 lands on one scaffold (dropped, :159); r3 is one contig; r4 closes against the stale previous line
+        assert got == b'scaffold_1\t10\t20\tr1/1\nscaffold_2\t30\t40\tr1/2\nscaffold_2\t9\t19\tr4/1\nscaffold_1\t3\t4\tr4/2\n'
+
+
+@pytest.mark.parametrize('refactor', [False, True])
+def test_stale_previous_line(eng, tmp_path, refactor):
+    """refactor variant: a same-contig line is skipped without becoming prev_line (refactor_breaks.py:150-151)."""
+    names, lengths = ['A', 'B'], [100, 200]
+    c2s = {'A': 'scaffold_1', 'B': 'scaffold_2'}
+    info = {'A': (0, 100, 'FOW'), 'B': (0, 200, 'REV')}
+    bed = b'A 1 2 x/1\nA 3 4 q/1\nA 5 6 q/1\nB 7 8 x/2\nB 9 10 z/2\nA 1 2 x/2\n'
+    got, want = both(eng, tmp_path, bed, names, lengths, c2s, info, refactor)
+    assert got == want
+    if refactor:
+        assert got == b'scaffold_1\t1\t2\tx/1\nscaffold_2\t192\t193\tx/2\n'
+    else:
+        assert got == b''
+
+
+def test_tile_boundaries(eng, tmp_path):
+    """Pairs on every side of the scanner's 32 KiB tiles, and a long run of same-contig lines."""
+    names, lengths = ['A', 'B', 'C'], [10 ** 6, 10 ** 6, 10 ** 6]
+    c2s = {'A': 'scaffold_1', 'B': 'scaffold_2'}
+    info = {'A': (0, 10 ** 6, 'REV'), 'B': (5, 5 + 10 ** 6, 'FOW')}
+    rows = []
+    for r in range(20000):
+        rows.append('A\t%d\t%d\tr%d/1' % (r, r + 30, r))
+        rows.append('%s\t%d\t%d\tr%d/2' % ('B' if r % 3 else 'A', r * 2, r * 2 + 7, r))
+        if r % 1000 == 0:
+            rows += ['C\t1\t2\tpad%d/1' % r] * 40
+    bed = ('\n'.join(rows) + '\n').encode()
+    for refactor in (False, True):
+        got, want = both(eng, tmp_path, bed, names, lengths, c2s, info, refactor)
+        assert got == want and len(got) > 100000
+
+
+@pytest.mark.parametrize('refactor', [False, True])
+@pytest.mark.parametrize('bed', [b'A 1 2 r/1\nB 1 2 r\n', b'A 1 2 r/1\nB 1 2\n', b'A 1 x r/1\nB 1 2 r/2\n', b'A 1 2 r/1\n\nB 1 2 r/2\n'])
+def test_errors_like_the_reference(eng, tmp_path, refactor, bed):
+    """IndexError (missing field or '/') and ValueError (int()) of the reference -> DataError."""
+    from salsa_b200.engine import DataError
+    names, lengths = ['A', 'B'], [100, 200]
+    c2s = {'A': 'scaffold_1', 'B': 'scaffold_2'}
+    info = {'A': (0, 100, 'FOW'), 'B': (0, 200, 'FOW')}
+    with pytest.raises((IndexError, ValueError)):
+        from oracle import py_twin
+        src = str(tmp_path / 's.bed')
+        open(src, 'wb').write(bed)
+        py_twin.reproject_bed(src, str(tmp_path / 'w.bed'), c2s, info, dict(zip(names, lengths)), refactor)
+    from salsa_b200 import reproject
+    with pytest.raises(DataError):
+        reproject.bed_pass(eng)(src, str(tmp_path / 'g.bed'), c2s, info, dict(zip(names, lengths)), refactor)
+
+
+def test_resident_product_feeds_make_links(eng, tmp_path):
+    """The BED a pass leaves in HBM is what make_links.py ingests next (no re-read of the file)."""
+    from salsa_b200 import reproject
+    names, lengths = ['A', 'B'], [100, 200]
+    c2s = {'A': 'scaffold_1', 'B': 'scaffold_2'}
+    info = {'A': (0, 100, 'FOW'), 'B': (0, 200, 'FOW')}
+    bed = b'A 1 2 r/1\nB 1 2 r/2\n'
+    got, want = both(eng, tmp_path, bed, names, lengths, c2s, info, False)
+    assert got == want
+    t = reproject.resident_bed(str(tmp_path / 'got.bed'), eng.device, load=False)
+    assert t is not None and bytes(t.cpu().numpy()) == got
+    open(str(tmp_path / 'got.bed'), 'ab').write(b'X 1 2 q/1\n')          # changed on disk: cache entry must not be used
+    assert reproject.resident_bed(str(tmp_path / 'got.bed'), eng.device, load=False) is None

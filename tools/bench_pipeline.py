@@ -4,8 +4,9 @@ BASELINE configs[0]: synthetic 2 Mb genome in 200 contigs, 1 M Hi-C pairs, -e GA
 
 Runs the drop-in run_pipeline.py twice over the same inputs: with the CUDA step programs
 (salsa_b200/bin) and with the CPU steps (oracle C port + compiled reference coverage tools; the
-reference's own Python-2 steps cannot run in this image).  The host-side steps (layout,
-re-projection, AGP) are the same code in both runs.  Prints one JSON line.
+reference's own Python-2 steps cannot run in this image; the BED re-projection is the oracle's
+Python twin).  The greedy layout, misjoin splitting and AGP writer are the same code in both runs.
+Prints one JSON line.
 """
 import json
 import os
@@ -55,8 +56,10 @@ def main():
         'gpu_path': {'wall_s': wg, 's_per_iteration': wg / ig, 'hot_steps_s': sum(sg.get(k, 0) for k in hot), 'steps_s': sg},
         'cpu_path': {'wall_s': wo, 's_per_iteration': wo / io, 'hot_steps_s': sum(so.get(k, 0) for k in hot), 'steps_s': so,
                      'kind': 'oracle C port + compiled reference break_contigs*, 1 core'},
-        'note': 'each GPU step is a fresh process (python + torch import + CUDA context, ~3-5 s) exactly like the reference spawns '
-                'its steps; at this tiny size that start-up dominates the GPU path.  Host-side Python steps are shared.'}))
+        'note': 'GPU path: the Python steps run inside run_pipeline.py (one CUDA context; RE_sites.py, the first GPU step, carries '
+                'the torch import + context creation), break_contigs* are separate C++ processes (one context each).  CPU path: '
+                'every step is a process, the BED re-projection inside layout_unitigs.py / refactor_breaks.py is the oracle twin '
+                '(pure Python).  The greedy layout, misjoin splitting and AGP writer are the same host code in both.'}))
 
 
 if __name__ == '__main__':
