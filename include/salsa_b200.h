@@ -392,6 +392,19 @@ int salsa_cov_analyse(const int32_t *d_diff, int32_t *d_cov, const salsa_cov_seg
                       void *stream);
 
 /*
+ * The two coverage programs as one call: main() of break_contigs_start.cpp:271-463
+ * (joins = 0; argv = -a BED -l LEN -s N) and of break_contigs.cpp:162-358
+ * (joins = 1; argv = -a BED -b BREAKPOINTS -l LEN -i N -s N), argv WITHOUT the
+ * program name, cmdline.h's short / --long=value / --long value forms.  The
+ * report the reference prints to stdout goes to out_path (NULL = stdout).
+ * d_bed != NULL: the BED (all nbytes of the -a file) is already in device
+ * memory and the file is not read.  Returns the exit status of the program
+ * (134 where the reference aborts on vector::at()).
+ */
+int salsa_break_contigs_run(int32_t joins, int32_t argc, const char *const *argv, const void *d_bed, size_t nbytes,
+                            const char *out_path);
+
+/*
  * Re-projection of the iteration-1 BED into scaffold coordinates: the BED
  * pass of update_bed, layout_unitigs.py:816-886 (refactor = 0) and
  * refactor_breaks.py:133-203 (refactor = 1).  The whole BED is resident at

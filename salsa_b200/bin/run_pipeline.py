@@ -106,18 +106,52 @@ def main(argv=None):
             open(redirect, 'w').close()
         return rc
 
+    def run_coverage_inprocess(step, words, redirect):
+        """break_contigs_start / break_contigs through the library call their main() wraps: same CUDA
+        context as the other steps, and the BED straight from HBM when a step left it there."""
+        import ctypes
+        if here not in sys.path:
+            sys.path.insert(0, here)
+        import _common
+        from salsa_b200 import _lib, reproject
+        eng = _common.engine()
+        argv = words[1:]
+        bed, ptr, nbytes = None, None, 0
+        if '-a' in argv:
+            try:
+                bed = reproject.resident_bed(argv[argv.index('-a') + 1], eng.device)
+            except (MemoryError, OSError):
+                bed = None                                   # too large to keep resident / missing: the call reads the file
+        if bed is not None and bed.numel():
+            ptr, nbytes = bed.data_ptr(), bed.numel()
+        arr = (ctypes.c_char_p * len(argv))(*[a.encode() for a in argv])
+        sys.stdout.flush()
+        return _lib.lib().salsa_break_contigs_run(int(step == 'break_contigs'), len(argv), arr, ptr, nbytes,
+                                                  redirect.encode() if redirect else None)
+
     def sh(cmd, fatal=True, cleanup=None):
         print(cmd)
         log.write(cmd + '\n')
         t0 = time.time()
         words = cmd.split()
         step = os.path.basename(words[1] if words[0] == py else words[0])
+        redirect = None
+        if inproc and not modules.get('started') and (step.endswith('.py') or step.startswith('break_contigs')):
+            # one-off: torch import, CUDA context, library load -- timed on its own line, not inside the first step
+            if here not in sys.path:
+                sys.path.insert(0, here)
+            import _common
+            _common.engine()
+            modules['started'] = True
+            timings.write('startup\t%.3f\n' % (time.time() - t0))
+            t0 = time.time()
+        if inproc and '>' in words and (words[0] == py or step in ('break_contigs', 'break_contigs_start')):
+            redirect = words[words.index('>') + 1]
+            words = words[:words.index('>')]
         if inproc and words[0] == py and step.endswith('.py'):
-            redirect = None
-            if '>' in words:
-                redirect = words[words.index('>') + 1]
-                words = words[:words.index('>')]
             rc, errtext = run_inprocess(words, redirect), ''
+        elif inproc and step in ('break_contigs', 'break_contigs_start'):
+            rc, errtext = run_coverage_inprocess(step, words, redirect), ''
         else:
             r = subprocess.run(cmd, shell=True, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
             rc, errtext = r.returncode, r.stdout + r.stderr
