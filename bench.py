@@ -31,8 +31,8 @@ UNIT = 'pairs/s'
 
 def ncu_traffic_ratio():
     """dram bytes (read + write) / algorithmic bytes of the ingest kernel, from the committed
-    `ncu --set full` capture (profiles/r01_v2_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
-    p = os.path.join(ROOT, 'profiles', 'r01_v2_ingest_metrics.txt')
+    `ncu --set full` capture (profiles/r01_v3_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
+    p = os.path.join(ROOT, 'profiles', 'r01_v3_ingest_metrics.txt')
     try:
         rd = wr = None
         for ln in open(p):
@@ -234,8 +234,19 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t[0])
     del hres
+    # the ceiling of that leg: the same pinned bytes through plain cudaMemcpyAsync in the same 64 MiB pieces
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    half = stage.numel() // 2
+    ev0.record()
+    for o in range(0, cut, half):
+        k = min(half, cut - o)
+        stage[:k].copy_(hbuf[o:o + k], non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    h2d_gbs = cut / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
     e2e_pairs = sample_lines / (nlines / pairs)
     e2e = {'value': e2e_pairs * world / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': int(cut), 'd2h_bytes_per_step': int(d2h),
+           'gbs': cut / e2e_s / 1e9, 'h2d_copy_only_gbs': h2d_gbs,
            'sample': 'first %d bytes of the same BED from pinned host memory via salsa_bed_ingest_dense_host '
                      '(64 MiB double-buffered chunks) + D2H of the compacted link list' % cut}
 
@@ -259,7 +270,7 @@ def run_ours(args):
                    'parity_full_size': 'table == generator expected table: %s; counted pairs %d' % (parity, stt.pairs)},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'traffic': (ncu_traffic_ratio() * bed_bytes) if ncu_traffic_ratio() else None,
-                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r01_v2_ingest_metrics.txt), '
+                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r01_v3_ingest_metrics.txt), '
                                        'scaled to this launch by algorithmic bytes',
                      'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
                      'kernel': 'bedscan::bed_scan_kernel<LinkPolicy<dense>>', 'algorithmic_bytes_per_launch': bed_bytes,

@@ -132,6 +132,36 @@ def bench_cov(eng, asm, dev, pairs):
     st = eng.stats_read()
     emit('cov_scan_start (BED -> diff arrays)', ms, bed.numel(), pairs=pairs, counted_pairs_per_pass=int(st.pairs // 4),
          note='BED text read once; +2 int32 atomics per accepted same-contig pair; includes zeroing %d MB of diff arrays' % (ndiff * 4 >> 20))
+    # ---- BED re-projection (update_bed pass) on the same BED: 3,000 contigs placed on 24 scaffolds, 10 % unplaced
+    from salsa_b200 import reproject
+    rng = np.random.default_rng(5)
+    nsc = 24
+    sc_of = rng.integers(0, nsc, n).astype(np.int32)
+    sc_of[rng.random(n) < 0.1] = -1
+    offs = np.zeros(n, dtype=np.int64)
+    acc = np.zeros(nsc, dtype=np.int64)
+    for i in range(n):
+        if sc_of[i] >= 0:
+            offs[i] = acc[sc_of[i]]
+            acc[sc_of[i]] += int(lens[i])
+    rev = (rng.random(n) < 0.5).astype(np.uint8)
+    snames = [b'scaffold_%d' % (k + 1) for k in range(nsc)]
+    for refactor in (False, True):
+        res = {}
+
+        def run_rp():
+            res['out'] = reproject.reproject(eng, bed, refactor, sc_of, offs, np.asarray(lens, np.int64), rev, snames)
+        ms = timed(run_rp)
+        out = res['out']
+        nl = int((out == 10).sum())
+        first = out.clone()
+        run_rp()
+        assert nl % 2 == 0 and torch.equal(first, res['out'])
+        emit('bed_reproject (%s variant: scan + sort + emit x2)' % ('refactor' if refactor else 'layout'), ms,
+             bed.numel() + out.numel(), pairs=pairs, kept_pairs=nl // 2, out_bytes=int(out.numel()),
+             note='BED read once by the candidate scan, candidate lines re-read by the two emit passes, output written once; '
+                  'includes two host round trips (candidate count, output size)', parity='deterministic; 2 lines per kept pair')
+        del out, first, res
     # parity property: every contig's differences sum to zero, coverage never negative
     ids = [i for i in range(n) if covoff[i] != coverage.NOSEED and touched[i]]
     segs = []
