@@ -230,12 +230,11 @@ class Engine:
         return ok, oc, m
 
     def _decode(self, ok, m):
-        keys = ok[:m].cpu().numpy().astype(np.uint64)
-        ends = (keys & np.uint64(3)).astype(np.uint8)
-        pair = keys >> np.uint64(2)
-        first = (pair // np.uint64(max(self.n, 1))).astype(np.int64)
-        second = (pair % np.uint64(max(self.n, 1))).astype(np.int64)
-        return first, second, ends
+        keys = ok[:m]                                  # < 2^63: n*n*4 cells
+        pair = keys >> 2
+        first = torch.div(pair, max(self.n, 1), rounding_mode='floor')
+        second = pair - first * max(self.n, 1)
+        return first.cpu().numpy(), second.cpu().numpy(), (keys & 3).to(torch.uint8).cpu().numpy()
 
     def links(self):
         """Compacted, key-sorted link list as numpy arrays (first, second, ends, count)."""
