@@ -5,9 +5,9 @@ bench.py's cpu_baseline / --impl reference legs.  The product package
 (salsa_b200/) never imports this module.
 
 Parity status is stated in oracle/salsa_oracle.c's header: the Python steps
-are "parity unpinned" by the reference's own tests (there are none; pinned by
-KATs + the py3 twin), the coverage steps are pinned against the compiled
-reference in oracle/_ref/.
+are pinned against vectors produced by the reference's own scripts under
+tests/golden/ref_py2emu.py (the reference has no tests of its own), the
+coverage steps against the compiled reference in oracle/_ref/.
 """
 import ctypes as C
 import os

@@ -5,8 +5,10 @@ TEST INFRASTRUCTURE ONLY (see oracle/salsa_oracle.c header): an independent
 second restatement used to cross-check the C oracle on small inputs.  Pure
 Python loops, so only for small cases.
 
-PARITY UNPINNED by the reference's own tests (it has none); the reference
-scripts are Python-2 only and cannot be imported here.  Deviations from a
+The reference has no tests of its own and its scripts are Python-2 only; parity of make_links /
+fast_scaled_scores / RE_sites is PINNED by tests/golden/links_ref.json, which the reference's own
+scripts produced under tests/golden/ref_py2emu.py (the twin and the C oracle both reproduce it;
+update_bed's pass and correct_links remain unpinned).  Deviations from a
 literal transliteration are exactly the Python-2 semantics that Python 3
 changed, each emulated explicitly:
   * ``str(float)``  -> ``py2_str`` ('%.12g' + '.0'),  evidence

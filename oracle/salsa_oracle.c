@@ -7,13 +7,18 @@
  *
  * PARITY STATUS
  *   - make_links / RE_sites / fast_scaled_scores: the reference is Python-2
- *     only and cannot run in this image (no python2, no lib2to3), and the
- *     reference tree holds no tests or golden vectors.  PARITY UNPINNED by the
- *     reference's own tests; pinned instead by (a) the two sample lines in
- *     fast_scaled_scores.py:39-40 (12-significant-digit serialisation),
- *     (b) hand-derived known-answer tests (tests/test_oracle_kat.py) and
- *     (c) agreement with the independent line-by-line py3 twin
- *     (oracle/py_twin.py).
+ *     only (no python2 and no lib2to3 in this image) and its tree holds no
+ *     tests or golden vectors.  PINNED against vectors produced by the
+ *     reference's OWN scripts, executed from /root/reference by
+ *     tests/golden/ref_py2emu.py, which restores the few Python-2 semantics
+ *     they rely on (print statements, long, iteritems, int/int floor
+ *     division, 12-digit str(float)) mechanically and leaves the program
+ *     logic to the reference's source text: tests/golden/links_ref.json
+ *     (+ make_golden.py, the generating script).  Also: the two sample lines
+ *     in fast_scaled_scores.py:39-40, hand-derived known-answer tests
+ *     (tests/test_oracle.py) and the independent line-by-line py3 twin
+ *     (oracle/py_twin.py).  What the emulation cannot restore is Python-2
+ *     dict order, so link files compare as sorted lines.
  *   - coverage (break_contigs_start / break_contigs): pinned against the
  *     UNMODIFIED reference sources compiled into oracle/_ref/ (oracle/Makefile)
  *     and against fixtures generated with those binaries (tests/golden/).

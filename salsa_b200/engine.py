@@ -191,7 +191,7 @@ class Engine:
                         k += 1
                 end = pos + (len(blk) - 1 - int(nl[k])) + 1
                 nxt = pos + (len(blk) - 1 - int(nl[k + 1])) + 1
-            dev = torch.from_numpy(np.ascontiguousarray(mm[pos:end])).to(self.device)
+            dev = torch.from_numpy(np.array(mm[pos:end])).to(self.device)      # a writable copy (torch refuses read-only maps)
             self.ingest_device(dev, base_offset=pos)
             torch.cuda.current_stream().synchronize()
             pos = nxt

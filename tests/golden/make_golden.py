@@ -6,10 +6,14 @@ been compiled by oracle/Makefile):   python tests/golden/make_golden.py
 coverage_ref.json : stdout of the UNMODIFIED reference programs
                     (oracle/_ref/break_contigs_start, break_contigs) on the
                     deterministic cases in tests/cases.py.
-links_twin.json   : the reference's Python steps cannot run here (Python 2
-                    only), so these vectors come from the line-by-line py3
-                    twin (oracle/py_twin.py) -- they pin the C oracle and the
-                    CUDA path against a second, independent restatement.
+links_twin.json   : vectors from the line-by-line py3 twin (oracle/py_twin.py),
+                    a second, independent restatement.
+links_ref.json    : the same vectors plus a messy-text case, produced by the
+                    reference's OWN Python-2 scripts executed from
+                    /root/reference by ref_py2emu.py (Python-2 semantics
+                    restored, program logic = the reference's source text).
+                    (+ messy_case.*.gz, its inputs.)
+make_pipeline_ref.py does the same for a whole two-iteration run.
 """
 import json
 import os
@@ -76,7 +80,63 @@ def main():
     out['links_avoid'] = sorted(py_twin.make_links(d + '/b.bed', d, 2))
     out['avoid'] = [['ctg000001', 'ctg000002'], ['ctg000003', 'ctg000007'], ['ctg000000', 'ctg000005']]
     json.dump(out, open(os.path.join(HERE, 'links_twin.json'), 'w'), indent=1, sort_keys=True)
+    json.dump(reference_vectors(d, out, bed, fa, asm.lengths_text()), open(os.path.join(HERE, 'links_ref.json'), 'w'),
+              indent=1, sort_keys=True)
     print('golden written')
+
+
+def reference_vectors(d, twin, bed, fa, lens_text):
+    """links_ref.json: the same vectors as links_twin.json, plus a messy-text case, produced by the
+    reference's OWN make_links.py / fast_scaled_scores.py / RE_sites.py executed from /root/reference
+    under the Python-2 emulation of ref_py2emu.py (read its header for what is emulated)."""
+    import gzip
+    import numpy as np
+    import ref_py2emu as R
+
+    def lines(path):
+        return sorted(open(path).read().splitlines(keepends=True))
+
+    ref = {'params': twin['params'], 'avoid': twin['avoid'], 'how': 'tests/golden/ref_py2emu.py over /root/reference/*.py'}
+    for enz in ('GATC', 'GATC,GANTC', 'DNASE', 'AAGCTT'):
+        text, rc = R.run('RE_sites.py', ['-a', d + '/a.fa', '-e', enz])
+        assert rc == 0
+        ref['re_' + enz] = text.splitlines()
+    r = tempfile.mkdtemp()
+    open(r + '/scaffold_length_iteration_1', 'wb').write(lens_text)
+    open(r + '/re_counts_iteration_1', 'w').write('\n'.join(ref['re_GATC,GANTC']) + '\n')
+    open(r + '/b.bed', 'wb').write(bed)
+    text, rc = R.run('make_links.py', ['-b', r + '/b.bed', '-d', r, '-i', '1'])
+    assert rc == 0
+    ref['links'], ref['links_stdout'] = lines(r + '/contig_links_iteration_1'), text
+    assert R.run('fast_scaled_scores.py', ['-d', r, '-i', '1'])[1] == 0
+    ref['scaled'] = lines(r + '/contig_links_scaled_iteration_1')
+    for f in ('scaffold_length', 're_counts'):
+        os.link(r + '/%s_iteration_1' % f, r + '/%s_iteration_2' % f)
+    open(r + '/links_avoid_iteration_2', 'w').write(''.join('%s\t%s\n' % tuple(p) for p in twin['avoid']))
+    assert R.run('make_links.py', ['-b', r + '/b.bed', '-d', r, '-i', '2'])[1] == 0
+    ref['links_avoid'] = lines(r + '/contig_links_iteration_2')
+    assert R.run('fast_scaled_scores.py', ['-d', r, '-i', '2'])[1] == 0
+    ref['scaled_avoid'] = lines(r + '/contig_links_scaled_iteration_2')
+    # messy text: whitespace variety, long names, signs, '\r', several '/', no final newline
+    rng = np.random.default_rng(77)
+    names = cases.MESSY_NAMES
+    L = [int(rng.integers(2000, 6000)) for _ in names]
+    mbed = cases.messy_bed(rng, names, 4000, L)
+    m = tempfile.mkdtemp()
+    mlen = b''.join(b'%s\t%d\n' % (nm, ln) for nm, ln in zip(names, L))
+    mre = b''.join(b'%s\t%d\t%d\n' % (nm, 3 + 2 * i, 40 - 3 * i) for i, nm in enumerate(names))
+    open(m + '/scaffold_length_iteration_1', 'wb').write(mlen)
+    open(m + '/re_counts_iteration_1', 'wb').write(mre)
+    open(m + '/b.bed', 'wb').write(mbed)
+    assert R.run('make_links.py', ['-b', m + '/b.bed', '-d', m, '-i', '1'])[1] == 0
+    assert R.run('fast_scaled_scores.py', ['-d', m, '-i', '1'])[1] == 0
+    ref['messy_links'] = lines(m + '/contig_links_iteration_1')
+    ref['messy_scaled'] = lines(m + '/contig_links_scaled_iteration_1')
+    for fn, blob in (('messy_case.bed.gz', mbed), ('messy_case.len.gz', mlen), ('messy_case.re.gz', mre)):
+        with open(os.path.join(HERE, fn), 'wb') as raw:
+            with gzip.GzipFile(fileobj=raw, mode='wb', mtime=0) as g:
+                g.write(blob)
+    return ref
 
 
 if __name__ == '__main__':

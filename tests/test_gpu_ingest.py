@@ -92,37 +92,13 @@ def test_random_cases(eng, oracle_lib, seed, mode):
     assert sum(want.values()) == int(counts.sum())
 
 
-def _messy_bed(rng, names, nlines, L):
-    """whitespace variety, long/short names, \\r\\n, extra columns, missing trailing newline"""
-    out = []
-    seps = [b'\t', b' ', b'  ', b'\t ', b' \t\t']
-    r = 0
-    for i in range(nlines):
-        if rng.random() < 0.6:
-            r += 1
-        c = names[int(rng.integers(0, len(names)))]
-        s = int(rng.integers(0, 5000))
-        e = s + int(rng.integers(1, 300))
-        sep = seps[int(rng.integers(0, len(seps)))]
-        rd = b'r%d' % r
-        if rng.random() < 0.7:
-            rd += b'/%d' % int(rng.integers(1, 3))
-        if rng.random() < 0.1:
-            rd += b'/x/y'
-        lead = b' ' if rng.random() < 0.05 else b''
-        tail = [b'', b'\t60\t+', b' extra col', b'\r', b'\t' * 3][int(rng.integers(0, 5))]
-        sg = b'+' if rng.random() < 0.05 else b''
-        out.append(lead + c + sep + sg + b'%d' % s + sep + b'%d' % e + sep + rd + tail)
-    return b'\n'.join(out)
-
-
 @pytest.mark.parametrize('seed', [0, 1, 2, 3])
 def test_messy_text(eng, oracle_lib, seed):
     rng = np.random.default_rng(seed)
-    names = [b'c', b'ctg1', b'ctg10', b'ctg2', b'a_very_long_contig_name_over_16_bytes_A', b'a_very_long_contig_name_over_16_bytes_B',
-             b'exactly16bytes__', b'exactly16bytes_', b'X' * 17, b'X' * 40, b'scaffold_12', b'Ctg1']
+    import cases
+    names = cases.MESSY_NAMES
     L = [int(rng.integers(2000, 6000)) for _ in names]
-    bed = _messy_bed(rng, names, 6000, L) + (b'\n' if seed % 2 else b'')
+    bed = cases.messy_bed(rng, names, 6000, L) + (b'\n' if seed % 2 else b'')
     want, _ = oracle_dict(oracle_lib, bed, names, L)
     assert len(want) > 50
     got, _ = gpu_dict(eng, bed, names, L)

@@ -142,3 +142,44 @@ def test_make_links_fails_like_reference(eng):
     with pytest.raises(DataError):
         make_links.main(['-b', d + '/b.bed', '-d', d, '-i', '1'])
     assert not os.path.exists(d + '/contig_links_iteration_1')
+
+
+def test_dropin_scripts_match_reference_vectors(eng):
+    """tests/golden/links_ref.json = output of the reference's OWN make_links.py / fast_scaled_scores.py /
+    RE_sites.py (run by tests/golden/ref_py2emu.py in the build container): the drop-in scripts must
+    write the same lines -- link order is Python-2 dict order in the reference, so sorted lines."""
+    import gzip
+    import io
+    import json
+    import make_links
+    import fast_scaled_scores
+    import RE_sites
+    gold = os.path.join(ROOT, 'tests', 'golden')
+    gz = lambda fn: gzip.open(os.path.join(gold, fn), 'rb').read()        # noqa: E731
+    g = json.load(open(os.path.join(gold, 'links_ref.json')))
+    lines = lambda p: sorted(open(p).read().splitlines(keepends=True))    # noqa: E731
+    d = tempfile.mkdtemp()
+    open(d + '/a.fa', 'wb').write(gz('links_case.fa.gz'))
+    for enz in ('GATC', 'GATC,GANTC', 'DNASE', 'AAGCTT'):
+        buf = io.StringIO()
+        assert RE_sites.main(['-a', d + '/a.fa', '-e', enz], out=buf) == 0
+        assert buf.getvalue().splitlines() == g['re_' + enz]
+    open(d + '/scaffold_length_iteration_1', 'wb').write(gz('links_case.len.gz'))
+    open(d + '/re_counts_iteration_1', 'w').write('\n'.join(g['re_GATC,GANTC']) + '\n')
+    open(d + '/b.bed', 'wb').write(gz('links_case.bed.gz'))
+    for f in ('scaffold_length', 're_counts'):
+        os.link(d + '/%s_iteration_1' % f, d + '/%s_iteration_2' % f)
+    open(d + '/links_avoid_iteration_2', 'w').write(''.join('%s\t%s\n' % tuple(p) for p in g['avoid']))
+    for it, lk, sk in ((1, 'links', 'scaled'), (2, 'links_avoid', 'scaled_avoid')):
+        assert make_links.main(['-b', d + '/b.bed', '-d', d, '-i', str(it)]) == 0
+        assert lines('%s/contig_links_iteration_%d' % (d, it)) == g[lk]
+        assert fast_scaled_scores.main(['-d', d, '-i', str(it)]) == 0
+        assert lines('%s/contig_links_scaled_iteration_%d' % (d, it)) == g[sk]
+    m = tempfile.mkdtemp()
+    open(m + '/scaffold_length_iteration_1', 'wb').write(gz('messy_case.len.gz'))
+    open(m + '/re_counts_iteration_1', 'wb').write(gz('messy_case.re.gz'))
+    open(m + '/b.bed', 'wb').write(gz('messy_case.bed.gz'))
+    assert make_links.main(['-b', m + '/b.bed', '-d', m, '-i', '1']) == 0
+    assert lines(m + '/contig_links_iteration_1') == g['messy_links']
+    assert fast_scaled_scores.main(['-d', m, '-i', '1']) == 0
+    assert lines(m + '/contig_links_scaled_iteration_1') == g['messy_scaled']

@@ -216,3 +216,50 @@ def test_cov_joins_golden(oracle_lib, case):
     names, L, bed = cases.coverage_case(seed, lens, holes, npairs, scaffold_style=True)
     bpn = {names[k]: v for k, v in bp.items()}
     assert _cov_join_lines(oracle_lib, names, L, bed, bpn) == g['joins'][case]
+
+
+def _ref_dirs(g, kind):
+    """-> directory prepared with the committed inputs of a links_ref.json case."""
+    d = tempfile.mkdtemp()
+    if kind == 'case':
+        open(d + '/scaffold_length_iteration_1', 'wb').write(gz('links_case.len.gz'))
+        open(d + '/re_counts_iteration_1', 'w').write('\n'.join(g['re_GATC,GANTC']) + '\n')
+        open(d + '/b.bed', 'wb').write(gz('links_case.bed.gz'))
+        for f in ('scaffold_length', 're_counts'):
+            os.link(d + '/%s_iteration_1' % f, d + '/%s_iteration_2' % f)
+        open(d + '/links_avoid_iteration_2', 'w').write(''.join('%s\t%s\n' % tuple(p) for p in g['avoid']))
+    else:
+        open(d + '/scaffold_length_iteration_1', 'wb').write(gz('messy_case.len.gz'))
+        open(d + '/re_counts_iteration_1', 'wb').write(gz('messy_case.re.gz'))
+        open(d + '/b.bed', 'wb').write(gz('messy_case.bed.gz'))
+    return d
+
+
+def test_golden_reference_vectors(oracle_lib):
+    """links_ref.json was produced by the reference's own scripts (tests/golden/ref_py2emu.py): the C
+    oracle and the py3 twin must both reproduce it, line for line."""
+    from oracle import py_twin
+    o = oracle_lib
+    g = json.load(open(os.path.join(GOLD, 'links_ref.json')))
+    fa = gz('links_case.fa.gz')
+    for enz in ('GATC', 'GATC,GANTC', 'DNASE', 'AAGCTT'):
+        n, l, r, s = o.re_sites(fa, enz)
+        assert ['%s %d %d' % (a.decode(), b, c) for a, b, c in zip(n, l, r)] == g['re_' + enz]
+    for impl in ('c', 'twin'):
+        d = _ref_dirs(g, 'case')
+        if impl == 'c':
+            links = lambda it: sorted(o.make_links_files(d + '/b.bed', d, it))        # noqa: E731
+            scaled = lambda it: sorted(o.fast_scaled_scores_files(d, it))             # noqa: E731
+        else:
+            def links(it):
+                ls = py_twin.make_links(d + '/b.bed', d, it)
+                open('%s/contig_links_iteration_%d' % (d, it), 'w').write(''.join(ls))
+                return sorted(ls)
+            scaled = lambda it: sorted(py_twin.fast_scaled_scores(d, it))             # noqa: E731
+        assert links(1) == g['links']
+        assert scaled(1) == g['scaled']
+        assert links(2) == g['links_avoid']
+        assert scaled(2) == g['scaled_avoid']
+        d = _ref_dirs(g, 'messy')
+        assert links(1) == g['messy_links']
+        assert scaled(1) == g['messy_scaled']
