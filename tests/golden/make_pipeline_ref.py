@@ -99,6 +99,24 @@ def main():
         for fn in ('links_avoid_iteration_%d', 'alignment_iteration_%d.bed', 'scaffold_length_iteration_%d', 're_counts_iteration_%d'):
             put_file('s%d.refactor.' % it + fn % (it + 1), d + '/' + fn % (it + 1))
 
+    # stage 0 (-m yes): correct.py with a hand-written input_breaks (three contigs cut; side outputs only,
+    # the stages below run on the uncut assembly)
+    c = w + '/clean'
+    os.makedirs(c)
+    lens = [ln.split() for ln in open(data + '/contigs.len')]
+    cuts = ''.join('%s\t%d\n' % (a[0], int(a[1]) * frac // 100) for a, frac in zip([lens[1], lens[7], lens[20]], (50, 25, 80)))
+    open(c + '/input_breaks', 'w').write(cuts)
+    ref('correct.py', data + '/assembly.fa', c + '/input_breaks', data + '/reads.bed', c)
+    put('s0.input_breaks', cuts.encode())
+    put_file('s0.alignment_iteration_1.tmp.bed', c + '/alignment_iteration_1.tmp.bed')
+    put_file('s0.asm.cleaned.fasta', c + '/asm.cleaned.fasta')
+    # correct.py only writes its BED buffer every 1,000,000 lines and never flushes the rest (correct.py:86-91):
+    # the BED above comes out empty.  Same step on the BED repeated 40 times (> 1 M lines); only the digest is kept.
+    import hashlib
+    open(c + '/big.bed', 'wb').write(open(data + '/reads.bed', 'rb').read() * 40)
+    assert R.run('correct.py', [data + '/assembly.fa', c + '/input_breaks', c + '/big.bed', c], as_function=True)[1] == 0
+    big = open(c + '/alignment_iteration_1.tmp.bed', 'rb').read()
+    put('s0.big40.digest', json.dumps(dict(sha256=hashlib.sha256(big).hexdigest(), bytes=len(big), lines=big.count(b'\n'))).encode())
     put('s1.re_counts_iteration_1', ref('RE_sites.py', '-a', d + '/assembly.cleaned.fasta', '-e', 'GATC').encode())
     open(d + '/re_counts_iteration_1', 'w').write(gzip.open(OUT + '/s1.re_counts_iteration_1.gz', 'rt').read())
     links(1)

@@ -76,10 +76,16 @@ def to_py3_text(src):
     return '\n'.join(out)
 
 
-def run(script, argv, stdin=None):
-    """Executes REF/script as __main__ with sys.argv = [script] + argv.  -> (stdout text, exit code)."""
+def run(script, argv, stdin=None, as_function=False):
+    """Executes REF/script as __main__ with sys.argv = [script] + argv.  -> (stdout text, exit code).
+    as_function: run the module body as a function body (same statements, names become locals).  Only for
+    speed: CPython 3 appends to a str in place for local names but copies it for module-level names, which
+    makes the reference's `oline += ...` accumulation quadratic on million-line inputs."""
     src = open(os.path.join(REF, script)).read()
-    tree = _Div().visit(ast.parse(to_py3_text(src), filename=script))
+    text = to_py3_text(src)
+    if as_function:
+        text = 'def _module_body():\n' + ''.join('    ' + ln + '\n' for ln in text.split('\n')) + '_module_body()\n'
+    tree = _Div().visit(ast.parse(text, filename=script))
     ast.fix_missing_locations(tree)
     code = compile(tree, os.path.join(REF, script), 'exec')
     g = {'__name__': '__main__', '__file__': os.path.join(REF, script), 'long': int, 'str': _py2_str, '_div': _div,

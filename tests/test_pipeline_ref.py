@@ -127,3 +127,20 @@ def test_agp_writer(tmp_path):
     agp.write_outputs(d + '/assembly.cleaned.fasta', d + '/final.p', d + '/out.fasta', d + '/out.agp')
     assert open(d + '/out.agp', 'rb').read() == get('final.scaffolds_FINAL.agp')
     assert open(d + '/out.fasta', 'rb').read() == get('final.scaffolds_FINAL.fasta')
+
+
+def test_cleaning_step(tmp_path):
+    """correct.py (-m yes): cut contigs, rewritten FASTA and BED -- including the reference's missing final
+    flush of the BED buffer (correct.py:86-91: anything after the last full million lines is dropped)."""
+    import hashlib
+    from salsa_b200.host import clean
+    d = stage(tmp_path, {'assembly.fa': 'in.assembly.fa', 'reads.bed': 'in.reads.bed', 'input_breaks': 's0.input_breaks'})
+    clean.clean(d + '/assembly.fa', d + '/input_breaks', d + '/reads.bed', d)
+    assert open(d + '/alignment_iteration_1.tmp.bed', 'rb').read() == get('s0.alignment_iteration_1.tmp.bed') == b''
+    assert open(d + '/asm.cleaned.fasta', 'rb').read() == get('s0.asm.cleaned.fasta')
+    open(d + '/big.bed', 'wb').write(get('in.reads.bed') * 40)
+    clean.clean(d + '/assembly.fa', d + '/input_breaks', d + '/big.bed', d)
+    big = open(d + '/alignment_iteration_1.tmp.bed', 'rb').read()
+    want = json.loads(get('s0.big40.digest'))
+    assert (len(big), big.count(b'\n'), hashlib.sha256(big).hexdigest()) == (want['bytes'], want['lines'], want['sha256'])
+    assert want['lines'] == 1000000
