@@ -27,6 +27,13 @@ import torch  # noqa: E402
 
 METRIC = 'hic_pairs_per_sec_into_link_table'
 UNIT = 'pairs/s'
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line goes to the process's real stdout; main() moved fd 1 to stderr so that nothing a
+    library prints there (NCCL's version banner) can end up next to it."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (line + '\n').encode())
 
 
 def ncu_traffic_ratio():
@@ -202,7 +209,7 @@ def run_ours(args):
     e2e = None
     if args.no_extras:
         if rank == 0:
-            print(json.dumps({'profile_run': True, 'kernel_ms': kern_ms, 'ms_per_step': total_ms / args.steps}))
+            emit(json.dumps({'profile_run': True, 'kernel_ms': kern_ms, 'ms_per_step': total_ms / args.steps}))
         return
     sample = min(bed.numel(), args.e2e_bytes)
     cut = int((bed[:sample] == 10).nonzero()[-1].item()) + 1
@@ -289,7 +296,7 @@ def run_ours(args):
     }
     if world == 1:
         out['cpu_baseline'] = cpu_baseline(bed, asm, nlines / pairs, args.cpu_sample_bytes, threads=1)
-    print(json.dumps(out))
+    emit(json.dumps(out))
 
 
 def cpu_baseline(bed, asm, lines_per_pair, sample_bytes, threads):
@@ -351,7 +358,7 @@ def run_reference(args):
                                       'byte-range sharded over %d threads' % (sample_pairs, threads)},
            'e2e': {'value': val, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
            'gpu_launches': 0, 'links': int(res['count'].sum())}
-    print(json.dumps(out))
+    emit(json.dumps(out))
 
 
 def main():
@@ -367,6 +374,10 @@ def main():
     ap.add_argument('--no-extras', action='store_true', help='timed region only (for ncu runs): no e2e / cpu legs')
     ap.add_argument('--ref-pairs', type=int, default=10_000_000)
     args = ap.parse_args()
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     if args.pairs is None:
         from salsa_b200 import synth
