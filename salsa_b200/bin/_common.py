@@ -7,6 +7,9 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 _ENGINE = None
+# set by run_pipeline.py when it runs the steps inside its own process: keep BEDs in HBM between steps and
+# write the re-projected BED files in the background (run_pipeline.py flushes them before it exits)
+KEEP_RESIDENT = False
 
 
 def engine():
@@ -21,4 +24,4 @@ def engine():
 def bed_pass():
     """The CUDA BED pass for salsa_b200.host.reproject.update_bed (no CPU alternative here)."""
     from salsa_b200 import reproject
-    return reproject.bed_pass(engine())
+    return reproject.bed_pass(engine(), background=KEEP_RESIDENT)

@@ -19,6 +19,7 @@ import sys
 
 import numpy as np
 
+import _common
 from _common import engine
 
 
@@ -67,11 +68,15 @@ def main(argv=None):
     eng.begin_links('auto')
     print('bedfile started', file=sys.stderr)
     from salsa_b200.reproject import resident_bed
-    bed = resident_bed(args.mapping, eng.device, load=False)      # left in HBM by the re-projection that wrote it
+    try:
+        # left in HBM by the re-projection that wrote it, or loaded now and kept for the re-projections to come
+        bed = resident_bed(args.mapping, eng.device, load=_common.KEEP_RESIDENT)
+    except MemoryError:
+        bed = None
     if bed is not None:
         eng.ingest_device(bed)
     else:
-        eng.ingest_file(args.mapping)
+        eng.ingest_file(args.mapping)      # streamed through a staging buffer; nothing stays on the device
     eng.stats_read()                      # raises DataError where the reference would raise
     print('bedfile loaded', file=sys.stderr)
     sc = eng.score_links()

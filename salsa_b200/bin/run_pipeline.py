@@ -38,7 +38,21 @@ def ng50_of(lengths, genome_size=0):
     return None
 
 
+def _flush_written_behind():
+    """BED files a step left to a background writer must be complete before anyone outside this process reads them."""
+    mod = sys.modules.get('salsa_b200.reproject')
+    if mod is not None:
+        mod.flush()
+
+
 def main(argv=None):
+    try:
+        return _main(argv)
+    finally:
+        _flush_written_behind()
+
+
+def _main(argv=None):
     here = os.path.dirname(os.path.abspath(__file__))
     ap = argparse.ArgumentParser(description="SALSA Iterative Pipeline")
     ap.add_argument('-a', '--assembly', required=True, help='Path to initial assembly')
@@ -124,6 +138,8 @@ def main(argv=None):
                 bed = None                                   # too large to keep resident / missing: the call reads the file
         if bed is not None and bed.numel():
             ptr, nbytes = bed.data_ptr(), bed.numel()
+        else:
+            reproject.flush()                                # the program is going to read the file itself
         arr = (ctypes.c_char_p * len(argv))(*[a.encode() for a in argv])
         sys.stdout.flush()
         return _lib.lib().salsa_break_contigs_run(int(step == 'break_contigs'), len(argv), arr, ptr, nbytes,
@@ -142,6 +158,7 @@ def main(argv=None):
                 sys.path.insert(0, here)
             import _common
             _common.engine()
+            _common.KEEP_RESIDENT = True      # BEDs stay in HBM between steps; their files are written behind (flushed at exit)
             modules['started'] = True
             timings.write('startup\t%.3f\n' % (time.time() - t0))
             t0 = time.time()
@@ -153,6 +170,8 @@ def main(argv=None):
         elif inproc and step in ('break_contigs', 'break_contigs_start'):
             rc, errtext = run_coverage_inprocess(step, words, redirect), ''
         else:
+            if '.bed' in cmd:
+                _flush_written_behind()
             r = subprocess.run(cmd, shell=True, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
             rc, errtext = r.returncode, r.stdout + r.stderr
         timings.write('%s\t%.3f\n' % (step, time.time() - t0))

@@ -4,10 +4,12 @@ salsa_reproject_candidates / salsa_sort_u64 / salsa_reproject_emit.
 
 The iteration-1 BED is read from disk once per process and then stays in HBM (every
 iteration re-projects it twice); the BED each pass produces also stays resident, so the
-make_links.py step that follows ingests it without touching the file again.
+make_links.py / break_contigs steps that follow take it from there, and its file -- the
+reference's resume contract -- is written behind their back (write_behind / flush).
 """
 import ctypes as C
 import os
+import threading
 
 import numpy as np
 import torch
@@ -15,14 +17,19 @@ import torch
 from ._lib import check
 from .engine import _blob
 
-_RESIDENT = {}          # realpath -> (size, mtime_ns, uint8 CUDA tensor)
+CHUNK = 64 << 20
+_RESIDENT = {}          # realpath -> (size, mtime_ns, uint8 CUDA tensor); size None while the file is still being written
+_WRITERS = {}           # realpath -> _Writer still running
 
 
 def resident_bed(path, device, load=True):
-    """uint8 CUDA tensor holding the file, from the cache when its size and mtime still match."""
+    """uint8 CUDA tensor holding the file: from the cache when the file's size and mtime still match (or when
+    this process is still writing that very file), else streamed in from disk."""
     rp = os.path.realpath(path)
-    st = os.stat(rp)
     hit = _RESIDENT.get(rp)
+    if hit and hit[0] is None and rp in _WRITERS and hit[2].device == device:
+        return hit[2]
+    st = os.stat(rp)
     if hit and hit[0] == st.st_size and hit[1] == st.st_mtime_ns and hit[2].device == device:
         return hit[2]
     if not load:
@@ -31,18 +38,117 @@ def resident_bed(path, device, load=True):
     if st.st_size * 3 > free:
         raise MemoryError('%s (%d bytes) does not fit the GPU beside its re-projection; chunked re-projection is not '
                           'implemented' % (path, st.st_size))
-    if st.st_size == 0:
-        t = torch.empty(0, dtype=torch.uint8, device=device)
-    else:
-        t = torch.from_numpy(np.fromfile(rp, dtype=np.uint8)).to(device)
+    t = _stream_in(rp, st.st_size, device)
     _remember(rp, st.st_size, st.st_mtime_ns, t)
     return t
+
+
+def _stream_in(rp, size, device):
+    """File -> device through two pinned 64 MiB buffers: the read of chunk k+1 overlaps the copy of chunk k."""
+    t = torch.empty(size, dtype=torch.uint8, device=device)
+    if size == 0:
+        return t
+    pin = [torch.empty(CHUNK, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    ev = [torch.cuda.Event(), torch.cuda.Event()]
+    with open(rp, 'rb', buffering=0) as f:
+        k, pos = 0, 0
+        while pos < size:
+            n = min(CHUNK, size - pos)
+            if k >= 2:
+                ev[k & 1].synchronize()                       # the copy that last used this buffer is done
+            view = pin[k & 1].numpy()[:n]
+            got = 0
+            while got < n:
+                r = f.readinto(memoryview(view)[got:])
+                if not r:
+                    raise IOError('%s changed size while being read' % rp)
+                got += r
+            t[pos:pos + n].copy_(pin[k & 1][:n], non_blocking=True)
+            ev[k & 1].record()
+            pos += n
+            k += 1
+    torch.cuda.current_stream().synchronize()
+    return t
+
+
+class _Writer(threading.Thread):
+    """Device tensor -> file in the background (pinned double buffer on a side stream), written to
+    `path.part` and renamed when complete, so a reader -- or a resumed run -- never sees half a file."""
+
+    def __init__(self, rp, t, ready):
+        super().__init__(daemon=True)
+        self.rp, self.t, self.ready, self.cancelled, self.error = rp, t, ready, False, None
+
+    def run(self):
+        try:
+            t, size = self.t, self.t.numel()
+            stream = torch.cuda.Stream(device=t.device)
+            pin = [torch.empty(min(CHUNK, max(size, 1)), dtype=torch.uint8).pin_memory() for _ in range(2)]
+            ev = [torch.cuda.Event(), torch.cuda.Event()]
+            with torch.cuda.stream(stream):
+                stream.wait_event(self.ready)
+                spans = [(o, min(CHUNK, size - o)) for o in range(0, size, CHUNK)]
+                with open(self.rp + '.part', 'wb', buffering=0) as f:
+                    for k, (o, n) in enumerate(spans[:1]):
+                        pin[0][:n].copy_(t[o:o + n], non_blocking=True)
+                        ev[0].record(stream)
+                    for k, (o, n) in enumerate(spans):
+                        if self.cancelled:
+                            break
+                        if k + 1 < len(spans):
+                            o2, n2 = spans[k + 1]
+                            pin[(k + 1) & 1][:n2].copy_(t[o2:o2 + n2], non_blocking=True)
+                            ev[(k + 1) & 1].record(stream)
+                        ev[k & 1].synchronize()
+                        f.write(memoryview(pin[k & 1].numpy()[:n]))
+                stream.synchronize()
+            if self.cancelled:
+                os.remove(self.rp + '.part')
+            else:
+                os.replace(self.rp + '.part', self.rp)
+        except Exception as e:           # reported by flush()
+            self.error = e
+
+
+def write_behind(path, t):
+    """Start writing t to `path` in the background; t stays the resident copy of that file.  A write of the
+    same path that is still running is abandoned (its content is about to be replaced)."""
+    rp = os.path.realpath(path)
+    old = _WRITERS.pop(rp, None)
+    if old is not None:
+        old.cancelled = True
+        old.join()
+    if os.path.lexists(rp):
+        os.remove(rp)
+    ready = torch.cuda.Event()
+    ready.record()
+    w = _Writer(rp, t, ready)
+    _WRITERS[rp] = w
+    _remember(rp, None, None, t)
+    w.start()
+
+
+def flush(path=None):
+    """Wait until the file(s) this process is writing are complete on disk (all of them when path is None).
+    Must precede anything outside this process that reads them."""
+    keys = [os.path.realpath(path)] if path is not None else list(_WRITERS)
+    for rp in keys:
+        w = _WRITERS.pop(rp, None)
+        if w is None:
+            continue
+        w.join()
+        if w.error is not None:
+            raise w.error
+        hit = _RESIDENT.get(rp)
+        if hit is not None and hit[0] is None:
+            st = os.stat(rp)
+            _RESIDENT[rp] = (st.st_size, st.st_mtime_ns, hit[2])
 
 
 def _remember(rp, size, mtime_ns, t):
     """Keeps the sources it was asked to load plus the newest product; older products go."""
     if t is not None and rp.endswith('.bed') and not _is_source(rp):
-        for k in [k for k in _RESIDENT if not _is_source(k)]:
+        for k in [k for k in _RESIDENT if not _is_source(k) and k not in _WRITERS]:
             del _RESIDENT[k]
     _RESIDENT.pop(rp, None)
     _RESIDENT[rp] = (size, mtime_ns, t)
@@ -101,8 +207,10 @@ def reproject(eng, bed, refactor, scaffold_of, offset, length, reversed_, scaf_n
     return out
 
 
-def bed_pass(eng):
-    """-> bed_pass(src, dst, c2s, info, contig_length, refactor) for salsa_b200.host.reproject.update_bed."""
+def bed_pass(eng, background=False):
+    """-> bed_pass(src, dst, c2s, info, contig_length, refactor) for salsa_b200.host.reproject.update_bed.
+    background: return while dst is still being written (the caller promises to flush() before anything
+    outside this process reads it); the device copy serves every reader inside the process meanwhile."""
     def run(src, dst, c2s, info, contig_length, refactor):
         names = [k.encode('latin-1') for k in contig_length]
         idx = eng.set_contigs(names, np.array([contig_length[k] for k in contig_length], dtype=np.int64))
@@ -122,9 +230,7 @@ def bed_pass(eng):
             rev[i] = info[contig][2] != 'FOW'
         bed = resident_bed(src, eng.device)
         out = reproject(eng, bed, refactor, scaffold_of, offset, length, rev, [k.encode('latin-1') for k in scaf_keys])
-        host = out.cpu().numpy()
-        with open(dst, 'wb') as f:
-            host.tofile(f)
-        st = os.stat(dst)
-        _remember(os.path.realpath(dst), st.st_size, st.st_mtime_ns, out)
+        write_behind(dst, out)
+        if not background:
+            flush(dst)
     return run

@@ -96,11 +96,19 @@ def write_dataset(d, ncontig, genome, len_lo, len_hi, npairs, seed, nchrom=3, wi
     """assembly.fa, contigs.len (fai-like), reads.bed (+ assembly.gfa) under d."""
     from salsa_b200 import synth
     asm = synth.make_assembly(ncontig, genome, len_lo, len_hi, nchrom=nchrom, seed=seed)
-    rec = synth.gen_records(asm, npairs, seed + 1, noise=0.03, triple=0.002)
     os.makedirs(d, exist_ok=True)
     open(d + '/assembly.fa', 'wb').write(synth.gen_fasta(asm))
     open(d + '/contigs.len', 'wb').write(asm.lengths_text())
-    open(d + '/reads.bed', 'wb').write(bytes(synth.format_bed(rec).numpy()))
+    with open(d + '/reads.bed', 'wb') as f:
+        if npairs <= 20_000_000:
+            rec = synth.gen_records(asm, npairs, seed + 1, noise=0.03, triple=0.002)
+            f.write(bytes(synth.format_bed(rec).numpy()))
+        else:                                # large benchmark inputs: generate on the GPU, 20 M pairs at a time
+            for done in range(0, npairs, 20_000_000):
+                m = min(20_000_000, npairs - done)
+                rec = synth.gen_records(asm, m, seed + 1 + done, device='cuda', read_id_base=done, noise=0.03, triple=0.002)
+                synth.format_bed(rec).cpu().numpy().tofile(f)
+                del rec
     if with_gfa:
         rng = np.random.default_rng(seed)
         lines = ['S\t%s\t*\tLN:i:%d' % (n.decode(), l) for n, l in zip(asm.names, asm.lengths)]

@@ -165,3 +165,32 @@ def test_resident_product_feeds_make_links(eng, tmp_path):
     assert t is not None and bytes(t.cpu().numpy()) == got
     open(str(tmp_path / 'got.bed'), 'ab').write(b'X 1 2 q/1\n')          # changed on disk: cache entry must not be used
     assert reproject.resident_bed(str(tmp_path / 'got.bed'), eng.device, load=False) is None
+
+
+def test_write_behind(eng, tmp_path):
+    """background=True: the pass returns while the file is still being written; readers inside the process get the
+    device copy, flush() completes the file, and a second write of the same path replaces a running one."""
+    from salsa_b200 import reproject
+    from oracle import py_twin
+    rng = np.random.default_rng(9)
+    names = ['ctg%d' % i for i in range(50)]
+    lengths = [int(x) for x in rng.integers(1000, 100000, 50)]
+    c2s, info = placement(rng, names, lengths, 6)
+    bed = random_bed(rng, names, lengths, 40000)
+    src, dst = str(tmp_path / 'alignment_iteration_1.bed'), str(tmp_path / 'alignment_iteration_2.bed')
+    open(src, 'wb').write(bed)
+    clen = dict(zip(names, lengths))
+    run = reproject.bed_pass(eng, background=True)
+    run(src, dst, c2s, info, clen, False)
+    t = reproject.resident_bed(dst, eng.device, load=False)
+    assert t is not None
+    layout_bytes = bytes(t.cpu().numpy())
+    run(src, dst, c2s, info, clen, True)                       # same path again: replaces the write in flight
+    t2 = reproject.resident_bed(dst, eng.device, load=False)
+    reproject.flush()
+    assert not os.path.exists(dst + '.part')
+    py_twin.reproject_bed(src, str(tmp_path / 'want_l.bed'), c2s, info, clen, False)
+    py_twin.reproject_bed(src, str(tmp_path / 'want_r.bed'), c2s, info, clen, True)
+    assert layout_bytes == open(str(tmp_path / 'want_l.bed'), 'rb').read()
+    assert open(dst, 'rb').read() == open(str(tmp_path / 'want_r.bed'), 'rb').read() == bytes(t2.cpu().numpy())
+    assert reproject.resident_bed(dst, eng.device, load=False) is t2          # still served from HBM after the flush

@@ -47,6 +47,11 @@ def main():
     obin = pu.make_oracle_bin(d + '/obin')
     args = ['-e', 'GATC', '-i', '3', '-m', 'no']
     wg, sg, ig = run(pu.BIN, data, d + '/gpu', args)
+    if '--gpu-only' in sys.argv:
+        print(json.dumps({'metric': 'seconds_per_pipeline_iteration', 'pairs': pairs, 'iterations_run': ig,
+                          'gpu_path': {'wall_s': wg, 'startup_s': sg.get('startup', 0.0),
+                                       's_per_iteration_after_startup': (sum(sg.values()) - sg.get('startup', 0.0)) / ig, 'steps_s': sg}}))
+        return
     wo, so, io = run(obin, data, d + '/cpu', args)
     same = open(d + '/gpu/scaffolds_FINAL.agp').read() == open(d + '/cpu/scaffolds_FINAL.agp').read()
     hot = ('make_links.py', 'fast_scaled_scores.py', 'RE_sites.py', 'break_contigs', 'break_contigs_start')
