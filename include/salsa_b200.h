@@ -419,20 +419,24 @@ int salsa_break_contigs_run(int32_t joins, int32_t argc, const char *const *argv
  *     Data errors (missing fields or '/', bad integers) land in d_stats as
  *     for the ingest; the reference raises IndexError / ValueError there.
  *  2. salsa_sort_u64 (CUB) puts them in file order = output order.
- *  3. salsa_reproject_emit with d_out == NULL writes each candidate's output
- *     byte count to d_out_off[k]; after salsa_exclusive_scan_u64 over
- *     ncand + 1 entries (last = 0 -> total) the same call with d_out writes
- *     "scaffold\tstart\tend\tread\n" twice per kept pair (:864-871).
+ *  3. salsa_reproject_emit works in blocks of 256 consecutive candidates
+ *     (nblk = salsa_reproject_blocks(ncand)).  With d_out == NULL it writes
+ *     each candidate's output byte count to d_len[ncand] and each block's to
+ *     d_blk[nblk] (and 0 to d_blk[nblk]); after salsa_exclusive_scan_u64 over
+ *     nblk + 1 entries (d_blk[nblk] = total) the same call with d_out
+ *     writes "scaffold\tstart\tend\tread\n" twice per kept
+ *     pair (:864-871).
  */
 int salsa_reproject_candidates(salsa_ctx *ctx, const void *d_bed, size_t nbytes, int32_t refactor,
                                const int32_t *d_scaffold_of, uint64_t *d_cand, size_t capacity,
                                uint64_t *d_count, uint64_t *d_stats, void *stream);
 int salsa_sort_u64(uint64_t *d_in, uint64_t *d_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream);
+size_t salsa_reproject_blocks(size_t ncand);
 int salsa_reproject_emit(salsa_ctx *ctx, const void *d_bed, size_t nbytes, int32_t refactor,
                          const uint64_t *d_cand, size_t ncand, const int32_t *d_scaffold_of,
                          const int64_t *d_offset, const int64_t *d_length, const uint8_t *d_reversed,
-                         const char *d_scaf_names, const uint32_t *d_scaf_name_off, uint64_t *d_out_off,
-                         void *d_out, size_t out_capacity, uint64_t *d_stats, void *stream);
+                         const char *d_scaf_names, const uint32_t *d_scaf_name_off, uint32_t *d_len,
+                         uint64_t *d_blk, void *d_out, size_t out_capacity, uint64_t *d_stats, void *stream);
 
 /*
  * Host-side text assembly (no float conversion happens here: text is built

@@ -70,7 +70,8 @@ SIGNATURES = {
     'salsa_reproject_candidates': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_void_p, c_void_p, c_size_t, c_void_p,
                                              c_void_p, c_void_p]),
     'salsa_sort_u64': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_size_t), c_void_p]),
-    'salsa_reproject_emit': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_void_p, c_size_t] + [c_void_p] * 8 +
+    'salsa_reproject_blocks': (c_size_t, [c_size_t]),
+    'salsa_reproject_emit': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_void_p, c_size_t] + [c_void_p] * 9 +
                              [c_size_t, c_void_p, c_void_p]),
     'salsa_fasta_span_lengths': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p,
                                            c_void_p, c_void_p]),

@@ -194,12 +194,14 @@ def reproject(eng, bed, refactor, scaffold_of, offset, length, reversed_, scaf_n
     tmp = torch.empty(tb.value + 16, dtype=torch.uint8, device=dev)
     check(L.salsa_sort_u64(cand.data_ptr(), srt.data_ptr(), n, tmp.data_ptr(), C.byref(tb), st))
     del cand, tmp
-    off = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    nblk = L.salsa_reproject_blocks(n)
+    lens = torch.empty(n, dtype=torch.int32, device=dev)
+    blk = torch.empty(nblk + 1, dtype=torch.int64, device=dev)
     args = (eng.ctx, bed.data_ptr(), bed.numel(), int(bool(refactor)), srt.data_ptr(), n, so.data_ptr(), of.data_ptr(),
-            ln.data_ptr(), rv.data_ptr(), sb.data_ptr(), sf.data_ptr(), off.data_ptr())
+            ln.data_ptr(), rv.data_ptr(), sb.data_ptr(), sf.data_ptr(), lens.data_ptr(), blk.data_ptr())
     check(L.salsa_reproject_emit(*args, None, 0, eng.stats.data_ptr(), st))
-    check(L.salsa_exclusive_scan_u64(off.data_ptr(), n + 1, st))
-    total = int(off[n].item())
+    check(L.salsa_exclusive_scan_u64(blk.data_ptr(), nblk + 1, st))
+    total = int(blk[nblk].item())
     eng.stats_read()
     out = torch.empty(total, dtype=torch.uint8, device=dev)
     if total:
