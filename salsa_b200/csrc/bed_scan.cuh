@@ -736,7 +736,7 @@ template <class Policy>
 constexpr size_t dyn_smem() { return Layout<Policy::AVOID>::TOTAL; }
 
 template <class Policy>
-__global__ void __launch_bounds__(NTHREADS, SALSA_MINBLOCKS) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
+__global__ void __launch_bounds__(NTHREADS, Policy::AVOID ? 4 : SALSA_MINBLOCKS) bed_scan_kernel(typename Policy::Args PA, ScanArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     Smem S;
