@@ -23,6 +23,14 @@ struct LinkPolicy {
     typedef LinkArgs Args;
     static constexpr bool AVOID = AVOID_;   // links_avoid_iteration_N present (make_links.py:29-35,72-74)
     static constexpr bool NEED_RFULL = false;
+#ifdef SALSA_NO_LAZY
+    static constexpr bool LAZY = false;
+#else
+    // two-phase warp loop (bed_scan.cuh): only pairs whose contig names differ and whose read names may be
+    // equal get the full parse; pair() below then sees exactly the records it always saw
+    static constexpr bool LAZY = !AVOID_;
+#endif
+    static __device__ __forceinline__ bool lazy_candidate(bool same_name, bool reads_may_equal) { return !same_name && reads_may_equal; }
     // make_links.py:78 compares read.split('/')[0]
     static __device__ __forceinline__ int read_cmp_len(int rslash, int /*rfull*/) { return rslash; }
 

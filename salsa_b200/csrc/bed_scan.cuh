@@ -47,6 +47,7 @@ constexpr int SPARE_OFF = HALO + TILE + HALO + 32;      // one spare line (avoid
 constexpr int SMEM_BYTES = SPARE_OFF + HALO + 64;
 constexpr int SPWORDS = SPARE_OFF / 32 + 8;   // special-byte bitmap, 1 bit per staged byte (+ guard words)
 constexpr int RW = 8;                  // read-name words carried per record (32 bytes)
+constexpr int QCAP = 72;               // lazy warp loop: per-warp queue of pending line indices (< 32 left + <= 31 new) + 8 bytes of bookkeeping
 
 struct ScanArgs {
     const uint8_t *abase;     // 16-byte aligned base (<= caller pointer)
@@ -77,6 +78,7 @@ struct Smem {
     Rec *carry;
     int *wcount;
     int *flagp;
+    uint8_t *queue;       // lazy policies: per-warp ring (QCAP bytes) of line indices waiting for the full parse
     // avoid mode only (Policy::AVOID)
     int *idv;             // per line entry: contig id | IDV_INVOLVED, -1 unknown
     Rec *ext;             // record of the effective previous line when it lies before the tile
@@ -417,6 +419,49 @@ __device__ __forceinline__ Rec parse_any(const ScanArgs &A, const Smem &S, int l
     return rec;
 }
 
+// ---- lazy warp loop, phase 1: a line's field layout without converting anything ----
+// nl == NOT_PLAIN: the line is not provably of the plain form (the conditions of parse_fast minus the digit
+// checks; names up to what fits the 64-byte window; read-name prefix of at least 8 bytes).  Otherwise: name
+// length, first 16 name bytes (zero padded), read-prefix length and the last 8 bytes of the read prefix.
+// Equal names <=> equal (nl, bytes); equal read prefixes => equal (rl, d0, d1).
+struct Shape {
+    uint32_t w0, w1, w2, w3, nl, rl, d0, d1;
+};
+constexpr uint32_t NOT_PLAIN = 0xFFFFu;
+
+__device__ __forceinline__ Shape line_shape(const Smem &S, int p, int sent)
+{
+    Shape h;
+    h.w0 = h.w1 = h.w2 = h.w3 = 0; h.nl = NOT_PLAIN; h.rl = h.d0 = h.d1 = 0;
+    const uint8_t *s = S.s;
+    int i = p >> 5, sh = p & 31;
+    uint32_t a0 = S.sp[i], a1 = S.sp[i + 1], a2 = S.sp[i + 2];
+    unsigned long long M = (unsigned long long)__funnelshift_r(a0, a1, sh) | ((unsigned long long)__funnelshift_r(a1, a2, sh) << 32);
+    if (M & 1ull) return h;
+    int p1 = __ffsll((long long)M) - 1;
+    M &= M - 1;
+    int p2 = __ffsll((long long)M) - 1;
+    M &= M - 1;
+    int p3 = __ffsll((long long)M) - 1;
+    M &= M - 1;
+    if (!M) return h;
+    int p4 = __ffsll((long long)M) - 1;
+    uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
+    int rl = p4 - p3 - 1;
+    bool ok = (c1 == 9u || c1 == 32u) && (c2 == 9u || c2 == 32u) && (c3 == 9u || c3 == 32u) &&
+              (c4 == 47u || c4 == 9u || c4 == 32u || c4 == 10u) && p2 - p1 > 1 && p3 - p2 > 1 && rl >= 8 && (p + p4) < sent;
+    if (!ok) return h;
+    window4(S, p, p1, h.w0, h.w1, h.w2, h.w3);
+    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(s);
+    int q = p + p4 - 8, a = q >> 2, shq = (q & 3) * 8;
+    uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2];
+    h.d0 = __funnelshift_r(x0, x1, shq);
+    h.d1 = __funnelshift_r(x1, x2, shq);
+    h.nl = (uint32_t)p1;
+    h.rl = (uint32_t)rl;
+    return h;
+}
+
 // ---- avoid list (links_avoid_iteration_N, make_links.py:29-35,72-74) ------
 // `continue` on an avoided contig pair leaves prev_line untouched, so the line a
 // pair is formed with is the last NON-SKIPPED line.  A line whose contig is in no
@@ -564,10 +609,10 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
         // No block barrier, no line-list compaction: the record of a step's last lane reaches the
         // next step by shuffle, and a warp's very first "previous" line is the last line start of
         // the nearest non-empty warp before it (or found by the backward search below).
-        if (cnt == 0) return;
+        if (cnt == 0 && !Policy::LAZY) return;
         const uint16_t *my = S.seg + warp * WCAP;
-        int prev_start;
-        {
+        int prev_start = 0;
+        if (cnt > 0) {
             int v = warp - 1;
             while (v >= 0 && S.wcount[v] == 0) v--;
             if (v >= 0) prev_start = S.seg[v * WCAP + S.wcount[v] - 1];
@@ -590,6 +635,110 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
             }
         }
         const int first_line_idx = (int)((long long)A.mis - sb);
+        if (Policy::LAZY) {
+            // Three phases.  Phase 1, every line: field layout only (line_shape) -- no name lookup, no digit
+            // conversion, no read-name packing; a pair of plain lines is dropped here unless the policy wants it
+            // (links: contig names differ and the read names may be equal).  What survives, and every pair with
+            // a line that is not plain, is queued per warp.  Phase 2: whenever a warp has 32 waiting it runs the
+            // ordinary path on them with all lanes busy (parse_any on both lines, Policy::pair).  Phase 3: what
+            // is left in the eight queues at the end (< 32 each) is spread over the whole CTA, again with full
+            // warps.  Results are identical by construction: phase 1 only drops pairs for which pair() neither
+            // counts nor reports.
+            uint8_t *q = S.queue + warp * QCAP;       // [0, 62) line indices, [64] leftover count, [66, 68) prev_start
+            int qn = 0;
+            const unsigned lt = (1u << lane) - 1u;
+            auto full_pair = [&](const uint16_t *seg, int kk, int pst) {
+                int ls = (int)seg[kk], ps = kk > 0 ? (int)seg[kk - 1] : pst;
+                Rec rec = parse_any<Policy>(A, S, ls, sent, trunc, true);
+                Rec pv = parse_any<Policy>(A, S, ps, sent, trunc, true);
+                uint64_t off = A.base_offset + (uint64_t)((long long)ls + sb - (long long)A.mis);
+                bool prev_is_first = sb <= 0 && ps == first_line_idx;
+                if (Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
+            };
+            for (int k0 = -1; k0 + 1 < cnt; k0 += 31) {
+                int k = k0 + lane;
+                int lstart = 0;
+                Shape h;
+                h.w0 = h.w1 = h.w2 = h.w3 = 0; h.nl = NOT_PLAIN; h.rl = h.d0 = h.d1 = 0;
+                if (k < cnt) {
+                    lstart = k < 0 ? prev_start : (int)my[k];
+                    h = line_shape(S, lstart, sent);
+                }
+                Shape ph;
+                ph.w0 = __shfl_up_sync(0xffffffffu, h.w0, 1); ph.w1 = __shfl_up_sync(0xffffffffu, h.w1, 1);
+                ph.w2 = __shfl_up_sync(0xffffffffu, h.w2, 1); ph.w3 = __shfl_up_sync(0xffffffffu, h.w3, 1);
+                ph.nl = __shfl_up_sync(0xffffffffu, h.nl, 1); ph.rl = __shfl_up_sync(0xffffffffu, h.rl, 1);
+                ph.d0 = __shfl_up_sync(0xffffffffu, h.d0, 1); ph.d1 = __shfl_up_sync(0xffffffffu, h.d1, 1);
+                int pstart = __shfl_up_sync(0xffffffffu, lstart, 1);
+                bool cand = false;
+                if (lane >= 1 && k < cnt) {
+                    nlines_acc++;
+                    if (h.nl == NOT_PLAIN || ph.nl == NOT_PLAIN) cand = true;
+                    else {
+                        bool same = ((h.nl ^ ph.nl) | (h.w0 ^ ph.w0) | (h.w1 ^ ph.w1) | (h.w2 ^ ph.w2) | (h.w3 ^ ph.w3)) == 0u;
+                        if (same && h.nl > 16u) same = bytes_equal_back(s, pstart + 16, lstart + 16, (int)h.nl - 16);
+                        bool rmay = ((h.rl ^ ph.rl) | (h.d0 ^ ph.d0) | (h.d1 ^ ph.d1)) == 0u;
+                        cand = Policy::lazy_candidate(same, rmay);
+                    }
+                }
+                unsigned m = __ballot_sync(0xffffffffu, cand);
+                if (cand) q[qn + __popc(m & lt)] = (uint8_t)k;
+                qn += __popc(m);
+                __syncwarp();
+                if (qn >= 32) {
+                    full_pair(my, (int)q[lane], prev_start);
+                    int r = qn - 32;                         // < 31: move them to the front
+                    uint8_t keep = lane < r ? q[32 + lane] : (uint8_t)0;
+                    __syncwarp();
+                    if (lane < r) q[lane] = keep;
+                    qn = r;
+                    __syncwarp();
+                }
+            }
+            if (lane == 0) {
+                q[64] = (uint8_t)qn;
+                *reinterpret_cast<uint16_t *>(q + 66) = (uint16_t)prev_start;
+            }
+            __syncthreads();
+            {
+                // two lanes per pair (the odd one parses the previous line) so that twice as many warps share
+                // the tail and the barrier above is held for half as long
+                int total = 0;
+#pragma unroll
+                for (int w = 0; w < NWARPS; w++) total += S.queue[w * QCAP + 64];
+                for (int base = 0; base < total; base += NTHREADS / 2) {
+                    if (base + (warp << 4) >= total) break;              // warp-uniform: none of this warp's pairs exist
+                    int t = base + (tid >> 1), w = 0, cw = S.queue[64];
+                    const bool valid = t < total;
+                    while (w < NWARPS - 1 && t >= cw) {
+                        t -= cw;
+                        w++;
+                        cw = S.queue[w * QCAP + 64];
+                    }
+                    Rec rec;
+                    rec.id = -1; rec.s_lo = rec.s_hi = rec.e_lo = rec.e_hi = 0; rec.name = rec.read = 0; rec.flags = 0;
+#pragma unroll
+                    for (int j = 0; j < RW; j++) rec.rw[j] = 0;
+                    int ls = 0, ps = 0;
+                    if (valid) {
+                        const uint8_t *qw = S.queue + w * QCAP;
+                        const uint16_t *seg = S.seg + w * WCAP;
+                        int kk = qw[t];
+                        ls = (int)seg[kk];
+                        ps = kk > 0 ? (int)seg[kk - 1] : (int)*reinterpret_cast<const uint16_t *>(qw + 66);
+                        rec = parse_any<Policy>(A, S, (lane & 1) ? ps : ls, sent, trunc, true);
+                    }
+                    Rec pv = rec_shfl_idx(rec, lane | 1);
+                    if (valid && !(lane & 1)) {
+                        uint64_t off = A.base_offset + (uint64_t)((long long)ls + sb - (long long)A.mis);
+                        bool prev_is_first = sb <= 0 && ps == first_line_idx;
+                        if (Policy::pair(PA, A, s, pv, rec, off, prev_is_first)) npairs_acc++;
+                    }
+                }
+            }
+            return;
+        }
+        if (cnt == 0) return;
         // steps overlap by one entry: lane 0 re-parses the previous step's last line and only plays
         // "previous" (1/32 more parsing, but no record has to live across steps)
         for (int k0 = -1; k0 + 1 < cnt; k0 += 31) {
@@ -725,7 +874,8 @@ struct Layout {
     static constexpr size_t OFF_SEG = OFF_SP + align16(SPWORDS * 4);
     static constexpr size_t OFF_MASK = OFF_SEG + align16(LCAP * 2);
     static constexpr size_t OFF_WCOUNT = OFF_MASK + align16(33 * RW * 4);
-    static constexpr size_t OFF_LINES = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));       // avoid mode only from here
+    static constexpr size_t OFF_QUEUE = OFF_WCOUNT + align16((NWARPS + 2) * sizeof(int));
+    static constexpr size_t OFF_LINES = OFF_QUEUE + (AV ? 0 : NWARPS * QCAP);                   // avoid mode only from here
     static constexpr size_t OFF_CARRY = OFF_LINES + align16((LCAP + 8) * 2);
     static constexpr size_t OFF_IDV = OFF_CARRY + align16((NWARPS + 1) * sizeof(Rec));
     static constexpr size_t OFF_EXT = OFF_IDV + align16((LCAP + 8) * sizeof(int));
@@ -747,7 +897,8 @@ __global__ void __launch_bounds__(NTHREADS, Policy::AVOID ? 4 : SALSA_MINBLOCKS)
     S.lowmask = reinterpret_cast<uint32_t (*)[RW]>(smem + LY::OFF_MASK);
     S.wcount = reinterpret_cast<int *>(smem + LY::OFF_WCOUNT);
     S.flagp = S.wcount + NWARPS;
-    S.lines = reinterpret_cast<uint16_t *>(smem + LY::OFF_LINES);      // the rest exists in avoid mode only
+    S.queue = smem + LY::OFF_QUEUE;
+    S.lines =reinterpret_cast<uint16_t *>(smem + LY::OFF_LINES);      // the rest exists in avoid mode only
     S.carry = reinterpret_cast<Rec *>(smem + LY::OFF_CARRY);
     S.idv = reinterpret_cast<int *>(smem + LY::OFF_IDV);
     S.ext = reinterpret_cast<Rec *>(smem + LY::OFF_EXT);
@@ -765,8 +916,10 @@ __global__ void __launch_bounds__(NTHREADS, Policy::AVOID ? 4 : SALSA_MINBLOCKS)
     const int sent = (int)(l1 - sb);                           // smem index of the sentinel
     const bool trunc = l1 < (long long)A.dend;
 
+    __shared__ uint32_t red[3];          // lines, counted pairs, warps done (epilogue)
     if (tid == 0) {
         *S.flagp = 0;
+        red[0] = red[1] = red[2] = 0;
         uint32_t b = smem_u32(&bar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -850,17 +1003,16 @@ __global__ void __launch_bounds__(NTHREADS, Policy::AVOID ? 4 : SALSA_MINBLOCKS)
         nlines += __shfl_xor_sync(0xffffffffu, nlines, d);
         npairs += __shfl_xor_sync(0xffffffffu, npairs, d);
     }
-    __shared__ uint32_t red[2];
-    if (tid == 0) red[0] = red[1] = 0;
-    __syncthreads();
+    // no barrier: every warp adds its sums in shared memory, the last one to do so owns the global update
     if ((tid & 31) == 0) {
         atomicAdd(&red[0], nlines);
         atomicAdd(&red[1], npairs);
-    }
-    __syncthreads();
-    if (tid == 0) {
-        if (red[0]) atomicAdd((unsigned long long *)&A.stats[1], (unsigned long long)red[0]);
-        if (red[1]) atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)red[1]);
+        __threadfence_block();
+        if (atomicAdd(&red[2], 1u) == NWARPS - 1) {
+            uint32_t tl = atomicAdd(&red[0], 0u), tp = atomicAdd(&red[1], 0u);
+            if (tl) atomicAdd((unsigned long long *)&A.stats[1], (unsigned long long)tl);
+            if (tp) atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)tp);
+        }
     }
 }
 

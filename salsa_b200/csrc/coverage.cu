@@ -48,6 +48,8 @@ template <bool JOINS>
 struct CovPolicy {
     typedef CovArgs Args;
     static constexpr bool NEED_RFULL = true;
+    static constexpr bool LAZY = false;
+    static __device__ __forceinline__ bool lazy_candidate(bool, bool) { return true; }
     static constexpr bool AVOID = false;
     // read.substr(0, len-2) == prev_read.substr(0, len-2)   (size_t wrap for len < 2: the whole string)
     static __device__ __forceinline__ int read_cmp_len(int /*rslash*/, int rfull) { return rfull >= 2 ? rfull - 2 : rfull; }

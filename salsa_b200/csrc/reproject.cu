@@ -56,6 +56,8 @@ struct CandPolicy {
     typedef CandArgs Args;
     static constexpr bool AVOID = false;
     static constexpr bool NEED_RFULL = true;
+    static constexpr bool LAZY = false;
+    static __device__ __forceinline__ bool lazy_candidate(bool, bool) { return true; }
     static __device__ __forceinline__ int read_cmp_len(int rslash, int /*rfull*/) { return rslash; }
 
     static __device__ __forceinline__ bool pair(const CandArgs &C, const ScanArgs &A, const uint8_t *s, const Rec &pv,
