@@ -545,43 +545,52 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint8_t *s = S.s;
     // ---- classify + newline scan: q in [lo, hi) -> line start q + 1 (valid iff q >= mis and q + 1 < dend)
+    // 32 bytes (two 16-byte chunks) per lane and iteration: one ballot / rank / store per 32 bytes
     const int nchunks = (int)((hi - lo) >> 4);
-    const int cpw = (nchunks + NWARPS - 1) / NWARPS;
+    const int npair = (nchunks + 1) >> 1;
+    const int ppw = (npair + NWARPS - 1) / NWARPS;
     int cnt = 0;                         // this warp's running count (uniform)
     const uint4 *s128 = reinterpret_cast<const uint4 *>(s);
     uint16_t *sp16 = reinterpret_cast<uint16_t *>(S.sp);
     // everything below in smem indices (int): a newline at index x counts iff vlo <= x < vhi
-    const int c0 = (int)((lo - sb) >> 4);                    // first chunk of the range
+    const int c0 = (int)((lo - sb) >> 4);                    // first chunk of the range (even: ranges start on 32 bytes)
     const long long vlo_ll = (long long)A.mis - sb, vhi_ll = (long long)A.dend - 1 - sb;
     const int vlo = vlo_ll < 0 ? 0 : (int)vlo_ll;
     const int vhi = vhi_ll > (long long)SMEM_BYTES ? SMEM_BYTES : (int)vhi_ll;
-    for (int it = 0; it < cpw; it += 32) {
-        int ch = warp * cpw + it + lane;
-        bool act = (it + lane) < cpw && ch < nchunks;
-        int ci = c0 + ch;
-        int x0 = ci << 4;                                    // smem index of chunk byte 0
-        uint32_t m16 = 0;
+    for (int it = 0; it < ppw; it += 32) {
+        int pr = warp * ppw + it + lane;
+        bool act = (it + lane) < ppw && pr < npair;
+        int ci = c0 + 2 * pr;
+        int x0 = ci << 4;                                    // smem index of the pair's byte 0
+        uint32_t m32 = 0;
         if (act) {
-            uint4 v = s128[ci];
-            m16 = nl16_of(v);
-            if (WRITE_SP) sp16[ci] = (uint16_t)sp16_of(v);
+            uint4 v0 = s128[ci];
+            if (2 * pr + 1 < nchunks) {
+                uint4 v1 = s128[ci + 1];
+                m32 = nl16_of(v0) | (nl16_of(v1) << 16);
+                if (WRITE_SP) S.sp[ci >> 1] = sp16_of(v0) | (sp16_of(v1) << 16);
+            } else {                                         // odd tail: the data ends inside this pair
+                m32 = nl16_of(v0);
+                if (WRITE_SP) sp16[ci] = (uint16_t)sp16_of(v0);
+            }
             // drop newlines outside the data or ending it (q + 1 < dend, q >= mis)
-            if (x0 < vlo || x0 + 16 > vhi) {
+            if (x0 < vlo || x0 + 32 > vhi) {
                 int a = vlo - x0, b = vhi - x0;
-                a = a < 0 ? 0 : (a > 16 ? 16 : a);
-                b = b < 0 ? 0 : (b > 16 ? 16 : b);
-                m16 &= b > a ? (((1u << b) - 1u) & ~((1u << a) - 1u)) : 0u;
+                a = a < 0 ? 0 : (a > 32 ? 32 : a);
+                b = b < 0 ? 0 : (b > 32 ? 32 : b);
+                uint32_t lowb = b >= 32 ? 0xFFFFFFFFu : ((1u << b) - 1u), lowa = a >= 32 ? 0xFFFFFFFFu : ((1u << a) - 1u);
+                m32 &= b > a ? (lowb & ~lowa) : 0u;
             }
         }
-        int sidx = x0 + 1;                     // smem index of the byte after chunk byte 0
-        unsigned has = __ballot_sync(0xffffffffu, m16 != 0u);
-        unsigned multi = __ballot_sync(0xffffffffu, (m16 & (m16 - 1u)) != 0u);
-        if (multi == 0u) {                     // at most one newline per 16-byte chunk: rank by ballot
+        int sidx = x0 + 1;                     // smem index of the byte after the pair's byte 0
+        unsigned has = __ballot_sync(0xffffffffu, m32 != 0u);
+        unsigned multi = __ballot_sync(0xffffffffu, (m32 & (m32 - 1u)) != 0u);
+        if (multi == 0u) {                     // at most one newline per 32 bytes: rank by ballot
             int pos = cnt + __popc(has & ((1u << lane) - 1u));
-            if (m16 && pos < WCAP) S.seg[warp * WCAP + pos] = (uint16_t)(sidx + __ffs(m16) - 1);
+            if (m32 && pos < WCAP) S.seg[warp * WCAP + pos] = (uint16_t)(sidx + __ffs(m32) - 1);
             cnt += __popc(has);
         } else {
-            int c = __popc(m16), inc = c;
+            int c = __popc(m32), inc = c;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 int o = __shfl_up_sync(0xffffffffu, inc, d);
@@ -589,9 +598,9 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
             }
             int pos = cnt + inc - c;
             int tot = __shfl_sync(0xffffffffu, inc, 31);
-            while (m16) {
-                int b = __ffs(m16) - 1;
-                m16 &= m16 - 1;
+            while (m32) {
+                int b = __ffs(m32) - 1;
+                m32 &= m32 - 1;
                 if (pos < WCAP) S.seg[warp * WCAP + pos] = (uint16_t)(sidx + b);
                 pos++;
             }
