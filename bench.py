@@ -38,8 +38,8 @@ def emit(line):
 
 def ncu_traffic_ratio():
     """dram bytes (read + write) / algorithmic bytes of the ingest kernel, from the committed
-    `ncu --set full` capture (profiles/r01_v3_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
-    p = os.path.join(ROOT, 'profiles', 'r01_v3_ingest_metrics.txt')
+    `ncu --set full` capture (profiles/r01_v4_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
+    p = os.path.join(ROOT, 'profiles', 'r01_v4_ingest_metrics.txt')
     try:
         rd = wr = None
         for ln in open(p):
@@ -285,7 +285,7 @@ def run_ours(args):
                    'parity_full_size': 'table == generator expected table: %s; counted pairs %d' % (parity, stt.pairs)},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'traffic': (ncu_traffic_ratio() * bed_bytes) if ncu_traffic_ratio() else None,
-                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r01_v3_ingest_metrics.txt), '
+                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r01_v4_ingest_metrics.txt), '
                                        'scaled to this launch by algorithmic bytes',
                      'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
                      'kernel': 'bedscan::bed_scan_kernel<LinkPolicy<dense>>', 'algorithmic_bytes_per_launch': bed_bytes,

@@ -41,7 +41,7 @@ def main():
             if m:
                 cur = (os.path.basename(m.group(1)), int(m.group(2)))
                 continue
-            if re.match(r'\s+/\*[0-9a-f]{4}\*/', ln):
+            if re.match(r'\s+/\*[0-9a-f]{4,}\*/', ln):
                 lines_of.append((cur, ln.strip()))
         if lines_of:
             break
