@@ -6,10 +6,11 @@
  * hot path sits behind process + file boundaries driven by run_pipeline.py
  * (SURVEY.md section 8(b)).  Each entry point below therefore cites the
  * reference PROGRAM (file:line of the loop) whose work it replaces; the
- * drop-in step scripts in salsa_b200/ (make_links.py, RE_sites.py,
- * fast_scaled_scores.py, break_contigs*.py) keep the reference's argv and
- * file formats and call these functions through ctypes.  INTEGRATION.md shows
- * the binding a maintainer of the reference would add.
+ * drop-in step programs in salsa_b200/bin/ (make_links.py, RE_sites.py,
+ * fast_scaled_scores.py, layout_unitigs.py, refactor_breaks.py through
+ * ctypes; break_contigs, break_contigs_start as C++ mains) keep the
+ * reference's argv and file formats and call these functions.
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
  *
  * Conventions
  *   - plain pointers and sizes only; no torch / C++ types.

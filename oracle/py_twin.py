@@ -7,8 +7,9 @@ Python loops, so only for small cases.
 
 The reference has no tests of its own and its scripts are Python-2 only; parity of make_links /
 fast_scaled_scores / RE_sites is PINNED by tests/golden/links_ref.json, which the reference's own
-scripts produced under tests/golden/ref_py2emu.py (the twin and the C oracle both reproduce it;
-update_bed's pass and correct_links remain unpinned).  Deviations from a
+scripts produced under tests/golden/ref_py2emu.py (the twin and the C oracle both reproduce it), and
+update_bed's BED pass by tests/golden/pipeline_ref/ (a stage-by-stage run of the reference's programs);
+correct_links remains unpinned (the reference needs boost::graph, absent here).  Deviations from a
 literal transliteration are exactly the Python-2 semantics that Python 3
 changed, each emulated explicitly:
   * ``str(float)``  -> ``py2_str`` ('%.12g' + '.0'),  evidence
