@@ -289,7 +289,11 @@ def run_ours(args):
                                        'scaled to this launch by algorithmic bytes',
                      'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
                      'kernel': 'bedscan::bed_scan_kernel<LinkPolicy<dense>>', 'algorithmic_bytes_per_launch': bed_bytes,
-                     'kernel_ms': kern_ms},
+                     'kernel_ms': kern_ms,
+                     'atomics_per_s': stt.pairs / (args.steps + args.warmup) / (kern_ms * 1e-3),
+                     'atomics_note': 'one 64-bit RED into the dense table per counted pair (L2); ~1 % of the ~2e11/s that '
+                                     'spread-address REDG sustains chip-wide (B300_MICROARCH.md: 1.29 cycles/lane/SM), so the '
+                                     'histogram is nowhere near an atomic limit and is not privatised in shared memory'},
         'e2e': e2e,
         'gpu_launches': args.steps * 1,
         'clocks': clocks,

@@ -36,8 +36,7 @@ def resident_bed(path, device, load=True):
         return None
     free, _ = torch.cuda.mem_get_info(device)
     if st.st_size * 3 > free:
-        raise MemoryError('%s (%d bytes) does not fit the GPU beside its re-projection; chunked re-projection is not '
-                          'implemented' % (path, st.st_size))
+        raise MemoryError('%s (%d bytes) is not kept on the GPU: it would not fit beside its re-projection' % (path, st.st_size))
     t = _stream_in(rp, st.st_size, device)
     _remember(rp, st.st_size, st.st_mtime_ns, t)
     return t
@@ -187,6 +186,7 @@ def reproject(eng, bed, refactor, scaffold_of, offset, length, reversed_, scaf_n
             break
         cap = n
     if n == 0:
+        eng.last_candidate = 0
         return torch.empty(0, dtype=torch.uint8, device=dev)
     srt = torch.empty(n, dtype=torch.int64, device=dev)
     tb = C.c_size_t(0)
@@ -202,6 +202,7 @@ def reproject(eng, bed, refactor, scaffold_of, offset, length, reversed_, scaf_n
     check(L.salsa_reproject_emit(*args, None, 0, eng.stats.data_ptr(), st))
     check(L.salsa_exclusive_scan_u64(blk.data_ptr(), nblk + 1, st))
     total = int(blk[nblk].item())
+    eng.last_candidate = int(srt[n - 1].item())       # refactor variant: offset of the last run start (chunked passes carry it)
     eng.stats_read()
     out = torch.empty(total, dtype=torch.uint8, device=dev)
     if total:
@@ -209,10 +210,46 @@ def reproject(eng, bed, refactor, scaffold_of, offset, length, reversed_, scaf_n
     return out
 
 
-def bed_pass(eng, background=False):
+def _chunked_pass(eng, src, dst, refactor, tables, chunk_bytes):
+    """The same pass for a BED that does not fit the GPU beside its product: line-aligned chunks streamed from
+    the file, the product appended to dst.  A chunk starts with the line that the sliding window still needs
+    from before it: the previous chunk's last line (layout variant) or its last run start (refactor variant:
+    the reference's prev_line only ever holds a run start, refactor_breaks.py:150-151,195)."""
+    size = os.path.getsize(src)
+    rp = os.path.realpath(dst)
+    flush(dst)
+    _RESIDENT.pop(rp, None)
+    carry = b''
+    with open(src, 'rb', buffering=0) as f, open(rp + '.part', 'wb') as out:
+        pos = 0
+        while pos < size:
+            blk = f.read(min(chunk_bytes, size - pos))
+            if pos + len(blk) < size:
+                cut = blk.rfind(b'\n') + 1
+                if cut == 0:
+                    raise ValueError('BED line longer than the re-projection chunk near byte %d' % pos)
+                blk = blk[:cut]
+                f.seek(pos + cut)
+            pos += len(blk)
+            data = carry + blk
+            t = torch.frombuffer(bytearray(data), dtype=torch.uint8).to(eng.device)
+            res = reproject(eng, t, refactor, *tables)
+            res.cpu().numpy().tofile(out)
+            if refactor:
+                a = eng.last_candidate                      # 0: the carried line is still the open run's start
+            else:
+                a = data.rfind(b'\n', 0, len(data) - 1) + 1 if data.endswith(b'\n') else data.rfind(b'\n') + 1
+            e = data.find(b'\n', a)
+            carry = data[a:e + 1] if e >= 0 else data[a:] + b'\n'
+            del t, res
+    os.replace(rp + '.part', rp)
+
+
+def bed_pass(eng, background=False, chunk_bytes=None):
     """-> bed_pass(src, dst, c2s, info, contig_length, refactor) for salsa_b200.host.reproject.update_bed.
     background: return while dst is still being written (the caller promises to flush() before anything
-    outside this process reads it); the device copy serves every reader inside the process meanwhile."""
+    outside this process reads it); the device copy serves every reader inside the process meanwhile.
+    chunk_bytes: force the chunked pass (default: only when the BED does not fit the GPU three times over)."""
     def run(src, dst, c2s, info, contig_length, refactor):
         names = [k.encode('latin-1') for k in contig_length]
         idx = eng.set_contigs(names, np.array([contig_length[k] for k in contig_length], dtype=np.int64))
@@ -230,8 +267,13 @@ def bed_pass(eng, background=False):
             scaffold_of[i] = sidx[key]
             offset[i] = info[contig][0]
             rev[i] = info[contig][2] != 'FOW'
+        tables = (scaffold_of, offset, length, rev, [k.encode('latin-1') for k in scaf_keys])
+        free, _ = torch.cuda.mem_get_info(eng.device)
+        if chunk_bytes is not None or (resident_bed(src, eng.device, load=False) is None and os.path.getsize(src) * 3 > free):
+            _chunked_pass(eng, src, dst, refactor, tables, chunk_bytes or (4 << 30))
+            return
         bed = resident_bed(src, eng.device)
-        out = reproject(eng, bed, refactor, scaffold_of, offset, length, rev, [k.encode('latin-1') for k in scaf_keys])
+        out = reproject(eng, bed, refactor, *tables)
         write_behind(dst, out)
         if not background:
             flush(dst)

@@ -194,3 +194,29 @@ def test_write_behind(eng, tmp_path):
     assert layout_bytes == open(str(tmp_path / 'want_l.bed'), 'rb').read()
     assert open(dst, 'rb').read() == open(str(tmp_path / 'want_r.bed'), 'rb').read() == bytes(t2.cpu().numpy())
     assert reproject.resident_bed(dst, eng.device, load=False) is t2          # still served from HBM after the flush
+
+
+@pytest.mark.parametrize('refactor', [False, True])
+@pytest.mark.parametrize('chunk', [700, 4096, 50000])
+def test_chunked_pass(eng, tmp_path, refactor, chunk):
+    """A BED that does not fit the GPU is re-projected in line-aligned chunks; each chunk starts with the line
+    the sliding window still needs (last line / last run start of the one before).  Forced here with tiny chunks,
+    over long same-contig runs that span several of them."""
+    from oracle import py_twin
+    from salsa_b200 import reproject
+    rng = np.random.default_rng(chunk)
+    names = ['ctg%d' % i for i in range(12)]
+    lengths = [int(x) for x in rng.integers(1000, 100000, 12)]
+    c2s, info = placement(rng, names, lengths, 4, unplaced=0.1)
+    parts = [random_bed(rng, names, lengths, 300, same=0.3)]
+    for k in range(6):
+        parts.append(('\n'.join('ctg3\t%d\t%d\tpad%d_%d/1' % (j, j + 9, k, j) for j in range(120)) + '\n').encode())
+        parts.append(random_bed(rng, names, lengths, 200, same=0.3))
+    bed = b''.join(parts)
+    src = str(tmp_path / 'alignment_iteration_1.bed')
+    open(src, 'wb').write(bed)
+    clen = dict(zip(names, lengths))
+    py_twin.reproject_bed(src, str(tmp_path / 'want.bed'), c2s, info, clen, refactor)
+    reproject.bed_pass(eng, chunk_bytes=chunk)(src, str(tmp_path / 'got.bed'), c2s, info, clen, refactor)
+    want = open(str(tmp_path / 'want.bed'), 'rb').read()
+    assert open(str(tmp_path / 'got.bed'), 'rb').read() == want and len(want) > 1000
