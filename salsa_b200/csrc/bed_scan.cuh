@@ -421,8 +421,8 @@ __device__ __forceinline__ Rec parse_any(const ScanArgs &A, const Smem &S, int l
 
 // ---- lazy warp loop, phase 1: a line's field layout without converting anything ----
 // nl == NOT_PLAIN: the line is not provably of the plain form (the conditions of parse_fast minus the digit
-// checks; names up to what fits the 64-byte window; read-name prefix of at least 8 bytes).  Otherwise: name
-// length, first 16 name bytes (zero padded), read-prefix length and the last 8 bytes of the read prefix.
+// checks; names up to what fits the 64-byte window).  Otherwise: name
+// length, first 16 name bytes (zero padded), read-prefix length and the last min(8, length) bytes of the read prefix.
 // Equal names <=> equal (nl, bytes); equal read prefixes => equal (rl, d0, d1).
 struct Shape {
     uint32_t w0, w1, w2, w3, nl, rl, d0, d1;
@@ -449,7 +449,7 @@ __device__ __forceinline__ Shape line_shape(const Smem &S, int p, int sent)
     uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
     int rl = p4 - p3 - 1;
     bool ok = (c1 == 9u || c1 == 32u) && (c2 == 9u || c2 == 32u) && (c3 == 9u || c3 == 32u) &&
-              (c4 == 47u || c4 == 9u || c4 == 32u || c4 == 10u) && p2 - p1 > 1 && p3 - p2 > 1 && rl >= 8 && (p + p4) < sent;
+              (c4 == 47u || c4 == 9u || c4 == 32u || c4 == 10u) && p2 - p1 > 1 && p3 - p2 > 1 && rl >= 1 && (p + p4) >= 8 && (p + p4) < sent;
     if (!ok) return h;
     window4(S, p, p1, h.w0, h.w1, h.w2, h.w3);
     const uint32_t *s32 = reinterpret_cast<const uint32_t *>(s);
@@ -457,6 +457,11 @@ __device__ __forceinline__ Shape line_shape(const Smem &S, int p, int sent)
     uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2];
     h.d0 = __funnelshift_r(x0, x1, shq);
     h.d1 = __funnelshift_r(x1, x2, shq);
+    if (rl < 8) {                                        // short read names: only their own bytes count
+        const uint32_t *mk = S.lowmask[8 - rl];
+        h.d0 &= ~mk[0];
+        h.d1 &= ~mk[1];
+    }
     h.nl = (uint32_t)p1;
     h.rl = (uint32_t)rl;
     return h;
