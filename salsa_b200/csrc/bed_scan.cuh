@@ -279,37 +279,59 @@ static __device__ __noinline__ Rec parse_line(const DevTable &t, const Smem &S, 
     return r;
 }
 
+// 64 bits of the special bitmap starting at smem index p
+__device__ __forceinline__ unsigned long long sp_window(const Smem &S, int p)
+{
+    int i = p >> 5, sh = p & 31;
+    uint32_t a0 = S.sp[i], a1 = S.sp[i + 1], a2 = S.sp[i + 2];
+    return (unsigned long long)__funnelshift_r(a0, a1, sh) | ((unsigned long long)__funnelshift_r(a1, a2, sh) << 32);
+}
+
+// The first four special bytes of the line at p (offsets relative to p).  A name longer than 16 bytes gets a
+// second window centred on its separator, so names up to 63 bytes and 63 more bytes of fields are in reach.
+// On return M's lowest set bit is p4's (relative to `base`): callers continue with M &= M - 1.
+__device__ __forceinline__ bool bounds4(const Smem &S, int p, int &p1, int &p2, int &p3, int &p4, unsigned long long &M, int &base)
+{
+    M = sp_window(S, p);
+    base = 0;
+    if ((M & 1ull) || !M) return false;
+    p1 = __ffsll((long long)M) - 1;
+    if (p1 > 16) {
+        base = p1;
+        M = sp_window(S, p + p1);
+    }
+    M &= M - 1;
+    p2 = base + __ffsll((long long)M) - 1;
+    M &= M - 1;
+    p3 = base + __ffsll((long long)M) - 1;
+    M &= M - 1;
+    if (!M) return false;
+    p4 = base + __ffsll((long long)M) - 1;
+    return true;
+}
+
 // ---- one line -> record, branch-free fast path.  Returns false when the line is not
 // provably of the plain form  name SEP digits SEP digits SEP read[/...]  (SEP = one tab
-// or space) with name <= 16, digits <= 12 bytes and all of it inside the staged bytes.
+// or space) with name <= 63, digits <= 12 bytes and all of it inside the staged bytes.
 template <bool NEED_RFULL>
 __device__ __forceinline__ bool parse_fast(const DevTable &t, const Smem &S, int p, int sent, Rec &r, int &rslash, int &rfull)
 {
     const uint8_t *s = S.s;
-    int i = p >> 5, sh = p & 31;
-    uint32_t a0 = S.sp[i], a1 = S.sp[i + 1], a2 = S.sp[i + 2];
-    unsigned long long M = (unsigned long long)__funnelshift_r(a0, a1, sh) | ((unsigned long long)__funnelshift_r(a1, a2, sh) << 32);
-    if (M & 1ull) return false;                          // leading whitespace / empty line
-    int p1 = __ffsll((long long)M) - 1;
-    M &= M - 1;
-    int p2 = __ffsll((long long)M) - 1;
-    M &= M - 1;
-    int p3 = __ffsll((long long)M) - 1;
-    M &= M - 1;
-    if (!M) return false;                                // fewer than four specials in 64 bytes
-    int p4 = __ffsll((long long)M) - 1;
+    unsigned long long M;
+    int p1, p2, p3, p4, base;
+    if (!bounds4(S, p, p1, p2, p3, p4, M, base)) return false;   // leading whitespace, empty line, < 4 specials in reach
     uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
     bool ok = (c1 == 9u || c1 == 32u) && (c2 == 9u || c2 == 32u) && (c3 == 9u || c3 == 32u) &&
               (c4 == 47u || c4 == 9u || c4 == 32u || c4 == 10u);
     int n1 = p2 - p1 - 1, n2 = p3 - p2 - 1, rl = p4 - p3 - 1;
-    ok = ok && p1 <= 16 && n1 >= 1 && n1 <= 12 && n2 >= 1 && n2 <= 12 && rl >= 1 && (p + p4) < sent;
+    ok = ok && n1 >= 1 && n1 <= 12 && n2 >= 1 && n2 <= 12 && rl >= 1 && (p + p4) < sent;
     rslash = rl;
     rfull = rl;
     if (NEED_RFULL) {
         if (c4 == 47u) {                                 // token continues after the first '/'
             M &= M - 1;
             if (!M) return false;
-            int p5 = __ffsll((long long)M) - 1;
+            int p5 = base + __ffsll((long long)M) - 1;
             uint32_t c5 = s[p + p5];
             ok = ok && (c5 == 9u || c5 == 32u || c5 == 10u) && (p + p5) < sent;
             rfull = p5 - p3 - 1;
@@ -327,7 +349,8 @@ __device__ __forceinline__ bool parse_fast(const DevTable &t, const Smem &S, int
     bool d2 = digits12(S, p + p3, n2, ve);
     if (!(d1 && d2)) return false;                       // signs, junk: let the full parser classify it
     r.name = (uint32_t)p | ((uint32_t)p1 << 16);
-    if (m0.x == (uint32_t)p1 && k0.x == w0 && k0.y == w1 && k0.z == w2 && k0.w == w3) r.id = (int)m0.y;   // p1 <= 16: exact
+    if (p1 <= 16 && m0.x == (uint32_t)p1 && k0.x == w0 && k0.y == w1 && k0.z == w2 && k0.w == w3) r.id = (int)m0.y;   // exact
+    else if (p1 > 16) r.id = lookup_words(t, s, w0, w1, w2, w3, p, p1);                                   // long name: verified against the blob
     else if (m0.x == 0xFFFFFFFFu) r.id = -1;
     else r.id = lookup_words(t, s, w0, w1, w2, w3, p, p1);                                                // collision: probe on
     r.s_lo = (int)(uint32_t)(unsigned long long)vs; r.s_hi = (int)(uint32_t)((unsigned long long)vs >> 32);
@@ -434,18 +457,9 @@ __device__ __forceinline__ Shape line_shape(const Smem &S, int p, int sent)
     Shape h;
     h.w0 = h.w1 = h.w2 = h.w3 = 0; h.nl = NOT_PLAIN; h.rl = h.d0 = h.d1 = 0;
     const uint8_t *s = S.s;
-    int i = p >> 5, sh = p & 31;
-    uint32_t a0 = S.sp[i], a1 = S.sp[i + 1], a2 = S.sp[i + 2];
-    unsigned long long M = (unsigned long long)__funnelshift_r(a0, a1, sh) | ((unsigned long long)__funnelshift_r(a1, a2, sh) << 32);
-    if (M & 1ull) return h;
-    int p1 = __ffsll((long long)M) - 1;
-    M &= M - 1;
-    int p2 = __ffsll((long long)M) - 1;
-    M &= M - 1;
-    int p3 = __ffsll((long long)M) - 1;
-    M &= M - 1;
-    if (!M) return h;
-    int p4 = __ffsll((long long)M) - 1;
+    unsigned long long M;
+    int p1, p2, p3, p4, base;
+    if (!bounds4(S, p, p1, p2, p3, p4, M, base)) return h;
     uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
     int rl = p4 - p3 - 1;
     bool ok = (c1 == 9u || c1 == 32u) && (c2 == 9u || c2 == 32u) && (c3 == 9u || c3 == 32u) &&
