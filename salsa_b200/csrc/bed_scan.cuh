@@ -303,9 +303,15 @@ __device__ __forceinline__ bool bounds4(const Smem &S, int p, int &p1, int &p2, 
     M &= M - 1;
     p2 = base + __ffsll((long long)M) - 1;
     M &= M - 1;
+    if (!M) return false;
     p3 = base + __ffsll((long long)M) - 1;
     M &= M - 1;
-    if (!M) return false;
+    if (!M) {                                            // long read name: a window centred on its separator
+        base = p3;
+        M = sp_window(S, p + p3);
+        M &= M - 1;
+        if (!M) return false;
+    }
     p4 = base + __ffsll((long long)M) - 1;
     return true;
 }

@@ -30,3 +30,5 @@ run('35 B names', base.replace(b'ctg', b'NODE_').replace(b'\t', b'_length_123456
 mid_names = [b'tig%08d_pilon_x' % i for i in range(3000)]
 run('19 B names', b'\n'.join(l.replace(b'ctg', b'tig00', 1).replace(b'\t', b'_pilon_x\t', 1) for l in base.split(b'\n')), mid_names)
 run('short reads r123/1', base.replace(b'read0000', b'r'), asm.names)
+run('38 B read names', base.replace(b'read0000', b'A00123:45:HXXXXXXXX:1:1101:12345:'), asm.names)
+run('4-column BED', b'\n'.join(l.rsplit(b'\t', 2)[0] for l in base.split(b'\n') if l) + b'\n', asm.names)
