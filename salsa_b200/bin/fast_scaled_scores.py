@@ -15,10 +15,43 @@ import sys
 
 import numpy as np
 
+import _common
 from _common import engine
 
 
-def scaled_text(eng, lines):
+def sort_order(eng, node_names, u, v, r_digits, r_exp10):
+    """The permutation `sort -k 5 -gr` (LC_ALL=C) puts the scaled lines in (run_pipeline.py:188,301), computed
+    with two stable radix sorts on the GPU.  sort compares field 5 as a number, descending; lines whose ratios
+    are equal fall to its last-resort comparison, the whole line bytewise, also reversed.  The ratio text is the
+    12-digit str(float), so (decimal exponent, 12-digit integer) orders it exactly; the line bytes are decided
+    by the two node names (every (u, v) occurs once, and a tab sorts below every name byte)."""
+    import torch
+    n = len(u)
+    order = sorted(range(len(node_names)), key=lambda i: node_names[i])
+    rank = np.empty(len(node_names), np.int64)
+    rank[order] = np.arange(len(node_names))
+    d = np.asarray(r_digits, np.int64)
+    key1 = np.where(d > 0, ((np.asarray(r_exp10, np.int64) + 512) << 40) | d, 0)
+    key2 = (rank[u] << 32) | rank[v]
+    dev, st = eng.device, torch.cuda.current_stream().cuda_stream
+
+    def gpu_sort(keys, vals):
+        k = torch.from_numpy(~keys).to(dev)                  # descending
+        ko, vo = torch.empty_like(k), torch.empty_like(vals)
+        tb = C.c_size_t(0)
+        eng.L.salsa_sort_pairs_u64(k.data_ptr(), vals.data_ptr(), ko.data_ptr(), vo.data_ptr(), n, None, C.byref(tb), st)
+        tmp = torch.empty(tb.value + 16, dtype=torch.uint8, device=dev)
+        rc = eng.L.salsa_sort_pairs_u64(k.data_ptr(), vals.data_ptr(), ko.data_ptr(), vo.data_ptr(), n, tmp.data_ptr(), C.byref(tb), st)
+        if rc:
+            raise RuntimeError(eng.L.salsa_last_error().decode())
+        return vo
+
+    idx = gpu_sort(key2, torch.arange(n, dtype=torch.int64, device=dev))           # ties of the next sort, in final order
+    idx = gpu_sort(key1[idx.cpu().numpy()], idx)                                   # stable: ratio decides, ties stay
+    return idx.cpu().numpy()
+
+
+def scaled_text(eng, lines, want_sorted=False):
     nodes = {}
     u = np.empty(len(lines), np.int32)
     v = np.empty(len(lines), np.int32)
@@ -40,7 +73,7 @@ def scaled_text(eng, lines):
         if w[i] < 0:
             raise ValueError('negative link weight: %r' % ln)
     if not len(lines):
-        return b''
+        return (b'', b'') if want_sorted else b''
     nn = len(nodes)
     res = eng.scaled_scores(u, v, w, nn)
     wd, wk, _ = eng.g12(w)                                         # str(w), :86
@@ -55,7 +88,15 @@ def scaled_text(eng, lines):
     nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], len(lines), out, cap)
     if nb < 0:
         raise RuntimeError(eng.L.salsa_last_error().decode())
-    return out.raw[:nb]
+    if not want_sorted:
+        return out.raw[:nb]
+    text = out.raw[:nb]
+    perm = sort_order(eng, list(nodes.keys()), u, v, res['r_digits'], res['r_exp10'])
+    arrs = [np.ascontiguousarray(a[perm]) for a in arrs]
+    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], len(lines), out, cap)
+    if nb < 0:
+        raise RuntimeError(eng.L.salsa_last_error().decode())
+    return text, out.raw[:nb]
 
 
 def main(argv=None):
@@ -65,7 +106,15 @@ def main(argv=None):
     args = parser.parse_args(argv)
     with open(args.directory + '/contig_links_iteration_' + str(args.iteration), 'rb') as f:
         lines = f.readlines()
-    text = scaled_text(engine(), lines)
+    if not _common.KEEP_RESIDENT:
+        text = scaled_text(engine(), lines)
+    else:
+        # inside run_pipeline.py: also leave the file its `sort -k 5 -gr` step would produce (GPU sort), which
+        # that step's resume rule then finds in place (run_pipeline.py:186-188)
+        text, srt = scaled_text(engine(), lines, want_sorted=True)
+        if srt:
+            with open(args.directory + '/contig_links_scaled_sorted_iteration_' + str(args.iteration), 'wb') as ofile:
+                ofile.write(srt)
     with open(args.directory + '/contig_links_scaled_iteration_' + str(args.iteration), 'wb') as ofile:
         ofile.write(text)
     return 0

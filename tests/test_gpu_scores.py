@@ -183,3 +183,36 @@ def test_dropin_scripts_match_reference_vectors(eng):
     assert lines(m + '/contig_links_iteration_1') == g['messy_links']
     assert fast_scaled_scores.main(['-d', m, '-i', '1']) == 0
     assert lines(m + '/contig_links_scaled_iteration_1') == g['messy_scaled']
+
+
+@pytest.mark.parametrize('seed', [1, 2, 3])
+def test_gpu_sort_equals_coreutils_sort(eng, seed):
+    """The sorted file the in-process pipeline leaves behind must be what `sort -k 5 -gr` (LC_ALL=C) writes:
+    ratio descending as a number, equal ratios by the whole line, bytewise, descending."""
+    import fast_scaled_scores
+    rng = np.random.default_rng(seed)
+    # names with prefix relations (ctg1 / ctg10 / ctg1_2), long names, and many exact ties (best buddies have ratio 1.0)
+    names = ['ctg%d' % i for i in range(40)] + ['ctg1_%d' % i for i in range(5)] + ['a_very_long_contig_name_%03d' % i for i in range(15)]
+    lines, seen = [], set()
+    for _ in range(3000):
+        a, b = (int(x) for x in rng.integers(0, len(names), 2))
+        if a == b or (min(a, b), max(a, b)) in seen:
+            continue
+        seen.add((min(a, b), max(a, b)))
+        w = [1.0, 0.5, 2.0, 1e-05, 12345.678, float(rng.integers(1, 50)) / float(rng.integers(1, 9))][int(rng.integers(0, 6))]
+        lines.append(('%s:%s\t%s:%s\t%s\t%d\n' % (names[a], 'BE'[int(rng.integers(2))], names[b], 'BE'[int(rng.integers(2))],
+                                               ('%.12g' % w) if '.' in ('%.12g' % w) or 'e' in ('%.12g' % w) else ('%.12g' % w) + '.0',
+                                               int(rng.integers(1, 999)))).encode())
+    # an edge may appear once per (u, v) NODE pair; drop duplicates of node pairs
+    uniq, out = set(), []
+    for ln in lines:
+        a = ln.split()
+        k = tuple(sorted((a[0], a[1])))
+        if k not in uniq and a[0] != a[1]:
+            uniq.add(k)
+            out.append(ln)
+    text, srt = fast_scaled_scores.scaled_text(eng, out, want_sorted=True)
+    want = subprocess.run(['sort', '-k', '5', '-gr'], input=text, capture_output=True, env=dict(os.environ, LC_ALL='C')).stdout
+    assert srt == want and len(srt) > 10000
+    ratios = [ln.split(b'\t')[4] for ln in srt.splitlines()]
+    assert max(ratios.count(r) for r in set(ratios)) > 50          # the tie rule really was exercised
