@@ -25,3 +25,22 @@ def bed_pass():
     """The CUDA BED pass for salsa_b200.host.reproject.update_bed (no CPU alternative here)."""
     from salsa_b200 import reproject
     return reproject.bed_pass(engine(), background=KEEP_RESIDENT)
+
+
+_LINKS = {}
+
+
+def remember_links(path, node_names, u, v, w, links):
+    """make_links.py -> fast_scaled_scores.py inside one process: the link list as arrays, valid while the file
+    it was written to is unchanged."""
+    st = os.stat(path)
+    _LINKS.clear()
+    _LINKS[os.path.realpath(path)] = (st.st_size, st.st_mtime_ns, (node_names, u, v, w, links))
+
+
+def cached_links(path):
+    hit = _LINKS.get(os.path.realpath(path))
+    if hit is None:
+        return None
+    st = os.stat(path)
+    return hit[2] if (hit[0], hit[1]) == (st.st_size, st.st_mtime_ns) else None

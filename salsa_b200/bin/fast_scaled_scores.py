@@ -51,7 +51,8 @@ def sort_order(eng, node_names, u, v, r_digits, r_exp10):
     return idx.cpu().numpy()
 
 
-def scaled_text(eng, lines, want_sorted=False):
+def parse_links(lines):
+    """contig_links_iteration_N lines -> (node names, u, v, w, links); fast_scaled_scores.py:35-60."""
     nodes = {}
     u = np.empty(len(lines), np.int32)
     v = np.empty(len(lines), np.int32)
@@ -72,28 +73,38 @@ def scaled_text(eng, lines, want_sorted=False):
         seen.add(e)
         if w[i] < 0:
             raise ValueError('negative link weight: %r' % ln)
-    if not len(lines):
+    return list(nodes.keys()), u, v, w, links
+
+
+def scaled_text(eng, lines, want_sorted=False):
+    return scaled_from_arrays(eng, *parse_links(lines), want_sorted=want_sorted)
+
+
+def scaled_from_arrays(eng, node_names, u, v, w, links, want_sorted=False):
+    """node_names: list[bytes] ('name:B' / 'name:E'), u / v: int32 node ids per link, w: float64 link weights as
+    the text file carries them (12 significant digits), links: int64 counts."""
+    n = len(u)
+    if not n:
         return (b'', b'') if want_sorted else b''
-    nn = len(nodes)
-    res = eng.scaled_scores(u, v, w, nn)
+    res = eng.scaled_scores(u, v, w, len(node_names))
     wd, wk, _ = eng.g12(w)                                         # str(w), :86
     from salsa_b200.engine import _blob
-    blob, off = _blob(list(nodes.keys()))
-    cap = len(lines) * 160 + 2 * sum(len(x) for x in lines) + 1024
+    blob, off = _blob(node_names)
+    cap = n * 160 + 2 * int(np.diff(off)[u].sum() + np.diff(off)[v].sum()) + 1024
     out = C.create_string_buffer(cap)
     c = lambda a, t: np.ascontiguousarray(a, t)                    # noqa: E731
     arrs = [c(u, np.int32), c(v, np.int32), c(wd, np.int64), c(wk, np.int32), c(res['b_digits'], np.int64),
             c(res['b_exp10'], np.int32), c(res['is_int1'], np.uint8), c(res['r_digits'], np.int64),
             c(res['r_exp10'], np.int32), c(links, np.int64)]
-    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], len(lines), out, cap)
+    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], n, out, cap)
     if nb < 0:
         raise RuntimeError(eng.L.salsa_last_error().decode())
     if not want_sorted:
         return out.raw[:nb]
     text = out.raw[:nb]
-    perm = sort_order(eng, list(nodes.keys()), u, v, res['r_digits'], res['r_exp10'])
+    perm = sort_order(eng, node_names, u, v, res['r_digits'], res['r_exp10'])
     arrs = [np.ascontiguousarray(a[perm]) for a in arrs]
-    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], len(lines), out, cap)
+    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], n, out, cap)
     if nb < 0:
         raise RuntimeError(eng.L.salsa_last_error().decode())
     return text, out.raw[:nb]
@@ -104,14 +115,19 @@ def main(argv=None):
     parser.add_argument("-i", "--iteration", help="iteration number")
     parser.add_argument("-d", '--directory', help="output directory")
     args = parser.parse_args(argv)
-    with open(args.directory + '/contig_links_iteration_' + str(args.iteration), 'rb') as f:
-        lines = f.readlines()
+    path = args.directory + '/contig_links_iteration_' + str(args.iteration)
     if not _common.KEEP_RESIDENT:
-        text = scaled_text(engine(), lines)
+        with open(path, 'rb') as f:
+            text = scaled_text(engine(), f.readlines())
     else:
-        # inside run_pipeline.py: also leave the file its `sort -k 5 -gr` step would produce (GPU sort), which
+        # inside run_pipeline.py: the links make_links.py just wrote are still in memory as arrays (no text to
+        # re-parse), and the file the `sort -k 5 -gr` step would produce is left behind as well (GPU sort), which
         # that step's resume rule then finds in place (run_pipeline.py:186-188)
-        text, srt = scaled_text(engine(), lines, want_sorted=True)
+        cached = _common.cached_links(path)
+        if cached is None:
+            with open(path, 'rb') as f:
+                cached = parse_links(f.readlines())
+        text, srt = scaled_from_arrays(engine(), *cached, want_sorted=True)
         if srt:
             with open(args.directory + '/contig_links_scaled_sorted_iteration_' + str(args.iteration), 'wb') as ofile:
                 ofile.write(srt)

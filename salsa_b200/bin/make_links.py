@@ -81,8 +81,17 @@ def main(argv=None):
     print('bedfile loaded', file=sys.stderr)
     sc = eng.score_links()
     print(sc['n'])
-    with open(args.directory + '/contig_links_iteration_' + iteration, 'wb') as ofile:
+    out_path = args.directory + '/contig_links_iteration_' + iteration
+    with open(out_path, 'wb') as ofile:
         ofile.write(eng.link_text(sc))
+    if _common.KEEP_RESIDENT and sc['n']:
+        # the next step re-reads this file; hand it the same numbers as arrays (w = float(str(score)), the value
+        # the text carries; node = contig end)
+        nodes = [nm + b':' + e for nm in eng.names for e in (b'B', b'E')]
+        u = (sc['first'] * 2 + (sc['ends'] >> 1)).astype(np.int32)
+        v = (sc['second'] * 2 + (sc['ends'] & 1)).astype(np.int32)
+        w = np.where(sc['is_int0'] != 0, 0.0, sc['w12'].cpu().numpy())
+        _common.remember_links(out_path, nodes, u, v, w, np.asarray(sc['count'], np.int64))
     return 0
 
 
