@@ -41,6 +41,18 @@ def test_config1_like(tmp_path, oracle_lib):
     assert any(fn.startswith('links_avoid_iteration_') for fn in g)
 
 
+def test_spawned_steps_equal_in_process_steps(tmp_path):
+    """--subprocess: every step its own process, as the reference runs them (files are the only hand-off: no
+    resident BEDs, no write-behind, coreutils sort) -- same directory content as the in-process default."""
+    data = str(tmp_path / 'data')
+    pu.write_dataset(data, ncontig=60, genome=700_000, len_lo=2_000, len_hi=40_000, npairs=60_000, seed=5, nchrom=3)
+    args = ['-e', 'GATC', '-i', '2', '-m', 'no']
+    run(pu.BIN, data, str(tmp_path / 'inproc'), args)
+    run(pu.BIN, data, str(tmp_path / 'spawned'), args + ['--subprocess'])
+    compare(str(tmp_path / 'inproc'), str(tmp_path / 'spawned'))
+    assert not [f for f in os.listdir(str(tmp_path / 'inproc')) if f.endswith('.part')]
+
+
 def test_misassembly_and_gfa(tmp_path, oracle_lib):
     """>= 1 Mb contigs so break_contigs_start / break_contigs do real work; -m yes, -g GFA, Arima enzymes."""
     data = str(tmp_path / 'data')
