@@ -12,8 +12,14 @@ _COMP = {'A': 'T', 'B': 'N', 'C': 'G', 'G': 'C', 'T': 'A', 'N': 'N', 'R': 'N', '
          'V': 'N', 'H': 'N', 'D': 'N', 'a': 't', 'c': 'g', 'g': 'c', 't': 'a', 'n': 'n', ' ': ''}
 
 
+_TABLE = str.maketrans(_COMP)
+
+
 def revcomp(s):
-    return ''.join(_COMP[b] for b in s)[::-1]      # KeyError on other characters, like the reference's table
+    bad = set(s) - _COMP.keys()
+    if bad:
+        raise KeyError(min(bad))                   # the reference's table lookup raises on other characters
+    return s.translate(_TABLE)[::-1]
 
 
 def original_coords(name, position, breaks):
