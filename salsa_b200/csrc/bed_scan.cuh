@@ -292,25 +292,36 @@ __device__ __forceinline__ unsigned long long sp_window(const Smem &S, int p)
 // On return M's lowest set bit is p4's (relative to `base`): callers continue with M &= M - 1.
 __device__ __forceinline__ bool bounds4(const Smem &S, int p, int &p1, int &p2, int &p3, int &p4, unsigned long long &M, int &base)
 {
-    M = sp_window(S, p);
+    const unsigned long long M0 = sp_window(S, p);
+    M = M0;
     base = 0;
-    if ((M & 1ull) || !M) return false;
+    if (M & 1ull) return false;                          // leading whitespace / empty line
+    // common case first, as straight-line code: short name, four specials inside the one window
     p1 = __ffsll((long long)M) - 1;
-    if (p1 > 16) {
-        base = p1;
-        M = sp_window(S, p + p1);
-    }
     M &= M - 1;
-    p2 = base + __ffsll((long long)M) - 1;
+    p2 = __ffsll((long long)M) - 1;
     M &= M - 1;
-    if (!M) return false;
-    p3 = base + __ffsll((long long)M) - 1;
+    p3 = __ffsll((long long)M) - 1;
     M &= M - 1;
-    if (!M) {                                            // long read name: a window centred on its separator
-        base = p3;
-        M = sp_window(S, p + p3);
+    if (!(M != 0ull && p1 <= 16)) {
+        if (!M0) return false;
+        M = M0;
+        if (p1 > 16) {                                   // long name: a window centred on its separator
+            base = p1;
+            M = sp_window(S, p + p1);
+        }
+        M &= M - 1;
+        p2 = base + __ffsll((long long)M) - 1;
         M &= M - 1;
         if (!M) return false;
+        p3 = base + __ffsll((long long)M) - 1;
+        M &= M - 1;
+        if (!M) {                                        // long read name: a window centred on its separator
+            base = p3;
+            M = sp_window(S, p + p3);
+            M &= M - 1;
+            if (!M) return false;
+        }
     }
     p4 = base + __ffsll((long long)M) - 1;
     return true;
