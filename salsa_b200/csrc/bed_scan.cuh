@@ -10,11 +10,11 @@
 //   * a tile OWNS the lines whose first byte lies in (t0, t1]; it evaluates the
 //     adjacent-line pairs whose second line it owns, so every pair is
 //     evaluated exactly once and the line at offset 0 only ever plays "previous";
-//   * CLASSIFY (cooperative, 16 bytes per lane, exact SWAR byte tests + dp4a bit
-//     packing): a bitmap of "special" bytes (<= 0x20 or '/') for the whole staged
-//     region, and the newline positions of the owned region, compacted into the
-//     list of line starts (ballot rank; a general warp scan when a 16-byte chunk
-//     holds two newlines);
+//   * CLASSIFY (cooperative, 32 bytes per lane and iteration, exact SWAR byte
+//     tests + dp4a bit packing): a bitmap of "special" bytes (<= 0x20 or '/') for
+//     the whole staged region, and the newline positions of the owned region,
+//     compacted into per-warp lists of line starts (ballot rank; a general warp
+//     scan when 32 bytes hold two newlines);
 //   * PARSE (one thread per line, branch-free fast path): the first four set
 //     bits of the special bitmap are the field boundaries; the contig name is
 //     looked up from a 16-byte unaligned window, start/end are converted 12
@@ -24,7 +24,12 @@
 //     through the byte-loop parser parse_line(), which implements str.split()
 //     in full -- results are identical, only speed differs;
 //   * the record travels to the next lane by warp shuffle -- the "previous
-//     line" -- and Policy::pair() decides what the adjacent pair contributes.
+//     line" -- and Policy::pair() decides what the adjacent pair contributes;
+//   * policies with LAZY = true (the link histogram) run that in three phases:
+//     every line only gets its field layout (line_shape); pairs that pair()
+//     provably neither counts nor reports are dropped there, the rest is queued
+//     and gets the full parse in batches of 32 per warp, then across the CTA
+//     (process_range, "Three phases").
 #pragma once
 #include "common.cuh"
 
