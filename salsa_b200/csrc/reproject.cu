@@ -176,16 +176,47 @@ __device__ __forceinline__ int ndigits(long long v)
            (w >= 100000000u) + (w >= 1000000000u);
 }
 
-__device__ __forceinline__ uint8_t *put_int(uint8_t *o, long long v)
+// Output bytes of one thread: 4-byte aligned words once the address is aligned (the words before and after
+// are shared with the neighbouring candidates' output, so the head and the tail go out byte by byte).
+struct Out {
+    uint8_t *p;
+    uint32_t acc;
+    bool al;
+    __device__ __forceinline__ void init(uint8_t *o) { p = o; acc = 0; al = false; }
+    __device__ __forceinline__ void put(uint32_t b)
+    {
+        uint32_t k = (uint32_t)(uintptr_t)p & 3u;
+        if (k == 0) al = true;
+        if (!al) *p = (uint8_t)b;
+        else {
+            acc |= b << (8 * k);
+            if (k == 3) { *reinterpret_cast<uint32_t *>(p - 3) = acc; acc = 0; }
+        }
+        p++;
+    }
+    __device__ __forceinline__ void flush()
+    {
+        uint32_t k = (uint32_t)(uintptr_t)p & 3u;
+        if (al) for (uint32_t j = 0; j < k; j++) p[(int)j - (int)k] = (uint8_t)(acc >> (8 * j));
+    }
+};
+
+__device__ __forceinline__ void put_int(Out &o, long long v)
 {
     unsigned long long u = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
-    if (v < 0) *o++ = '-';
-    int n = ndigits((long long)u);
-    uint8_t *e = o + n;
-    while (u >> 32) { *--e = (uint8_t)('0' + (int)(u % 10ull)); u /= 10ull; }     // rare: beyond 4.29e9
+    if (v < 0) o.put('-');
+    if (u >> 32) {                                       // rare: beyond 4.29e9
+        char buf[20];
+        int n = 0;
+        do { buf[n++] = (char)('0' + (int)(u % 10ull)); u /= 10ull; } while (u);
+        while (n) o.put((uint32_t)buf[--n]);
+        return;
+    }
     uint32_t w = (uint32_t)u;
-    do { uint32_t q = w / 10u; *--e = (uint8_t)('0' + (w - q * 10u)); w = q; } while (e > o);
-    return o + n;
+    unsigned long long bcd = 0;                          // digits as nibbles, most significant in the lowest nibble
+    int n = 0;
+    do { uint32_t q = w / 10u; bcd = (bcd << 4) | (w - q * 10u); w = q; n++; } while (w);
+    for (; n; n--) { o.put('0' + (uint32_t)(bcd & 15ull)); bcd >>= 4; }
 }
 
 __device__ __forceinline__ void mapped(const EmitArgs &E, const GLine &g, long long &a, long long &b)
@@ -195,18 +226,17 @@ __device__ __forceinline__ void mapped(const EmitArgs &E, const GLine &g, long l
     else { a = off + g.a; b = off + g.b; }
 }
 
-__device__ __forceinline__ uint8_t *put_line(const EmitArgs &E, uint8_t *o, const GLine &g, int sc, long long a, long long b)
+__device__ __forceinline__ void put_line(const EmitArgs &E, Out &o, const GLine &g, int sc, long long a, long long b)
 {
     uint32_t s0 = E.soff[sc], s1 = E.soff[sc + 1];
-    for (uint32_t i = s0; i < s1; i++) *o++ = (uint8_t)E.sblob[i];
-    *o++ = '\t';
-    o = put_int(o, a);
-    *o++ = '\t';
-    o = put_int(o, b);
-    *o++ = '\t';
-    for (int i = 0; i < g.tlen; i++) *o++ = E.bed[g.tok + i];
-    *o++ = '\n';
-    return o;
+    for (uint32_t i = s0; i < s1; i++) o.put((uint8_t)E.sblob[i]);
+    o.put('\t');
+    put_int(o, a);
+    o.put('\t');
+    put_int(o, b);
+    o.put('\t');
+    for (int i = 0; i < g.tlen; i++) o.put(E.bed[g.tok + i]);
+    o.put('\n');
 }
 
 constexpr int EB = 256;                 // candidates per block
@@ -282,8 +312,11 @@ __global__ void __launch_bounds__(EB) reproj_emit_kernel(EmitArgs E)
     if (n) {
         // direct byte stores: measured faster than assembling the block's piece in shared memory first, whose
         // 40 KB per block shrink the L1 that the per-thread byte loads of the two source lines live in
-        uint8_t *o = put_line(E, E.out + gbase + lo, p, sp, pa, pb);
+        Out o;
+        o.init(E.out + gbase + lo);
+        put_line(E, o, p, sp, pa, pb);
         put_line(E, o, c, sc, ca, cb);
+        o.flush();
     }
 }
 
