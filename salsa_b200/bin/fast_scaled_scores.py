@@ -76,8 +76,42 @@ def parse_links(lines):
     return list(nodes.keys()), u, v, w, links
 
 
+def parse_links_canonical(data):
+    """The same result as parse_links(data.splitlines()) without a Python statement per line, for files in the
+    form make_links.py writes them (exactly `u\tv\tscore\tcount\n`).  Returns None for anything else -- other
+    whitespace, empty or extra fields, duplicate / self edges, negative weights -- and the caller falls back to
+    the line loop, which also raises the right error."""
+    if not data or any(c in data for c in (b' ', b'\r', b'\x0b', b'\x0c')) or b'\t\t' in data or b'\n\t' in data \
+            or b'\t\n' in data or b'\n\n' in data or data[:1] in (b'\t', b'\n') or data[-1:] == b'\t':
+        return None
+    lines = data.split(b'\n')
+    if lines[-1] == b'':
+        lines.pop()
+    if not all(ln.count(b'\t') == 3 for ln in lines):
+        return None
+    toks = data.split()
+    n = len(lines)
+    if len(toks) != 4 * n:
+        return None
+    nodes = {}
+    try:
+        u = np.array([nodes.setdefault(x, len(nodes)) for x in toks[0::4]], dtype=np.int64)
+        v = np.array([nodes.setdefault(x, len(nodes)) for x in toks[1::4]], dtype=np.int64)
+        w = np.array(list(map(float, toks[2::4])), dtype=np.float64)
+        links = np.array(list(map(int, toks[3::4])), dtype=np.int64)
+    except (ValueError, OverflowError):
+        return None
+    key = (np.minimum(u, v) << 32) | np.maximum(u, v)
+    if (u == v).any() or (w < 0).any() or len(np.unique(key)) != n:
+        return None
+    return list(nodes.keys()), u.astype(np.int32), v.astype(np.int32), w, links
+
+
 def scaled_text(eng, lines, want_sorted=False):
-    return scaled_from_arrays(eng, *parse_links(lines), want_sorted=want_sorted)
+    parsed = parse_links_canonical(b''.join(lines))
+    if parsed is None:
+        parsed = parse_links(lines)
+    return scaled_from_arrays(eng, *parsed, want_sorted=want_sorted)
 
 
 def scaled_from_arrays(eng, node_names, u, v, w, links, want_sorted=False):
@@ -126,7 +160,11 @@ def main(argv=None):
         cached = _common.cached_links(path)
         if cached is None:
             with open(path, 'rb') as f:
-                cached = parse_links(f.readlines())
+                data = f.read()
+            cached = parse_links_canonical(data)
+            if cached is None:
+                parts = data.split(b'\n')                      # what readlines() yields in binary mode
+                cached = parse_links([p + b'\n' for p in parts[:-1]] + ([parts[-1]] if parts[-1] else []))
         text, srt = scaled_from_arrays(engine(), *cached, want_sorted=True)
         if srt:
             with open(args.directory + '/contig_links_scaled_sorted_iteration_' + str(args.iteration), 'wb') as ofile:
