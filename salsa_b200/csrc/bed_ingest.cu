@@ -6,7 +6,10 @@
 // is bed_scan.cuh; this file supplies what an adjacent pair contributes:
 // one 64-bit RED into the dense table, or one insert into the sparse table.
 // HBM traffic = the BED bytes once; everything else lives in smem / L2.
+#include <stdlib.h>
+
 #include "bed_scan.cuh"
+#include "bed_stream.cuh"
 
 namespace {
 
@@ -88,6 +91,38 @@ struct LinkPolicy {
     }
 };
 
+// what a counted pair does to the table, for the streaming scanner (bed_stream.cuh)
+template <bool SPARSE>
+struct LinkEmit {
+    typedef LinkArgs Args;
+    static __device__ __forceinline__ void emit(const LinkArgs &L, const ScanArgs &A, uint64_t key, uint64_t line_off)
+    {
+        LinkPolicy<SPARSE, false>::emit(L, A, key, line_off);
+    }
+};
+
+// SALSA_TILE_SCANNER=1 keeps the tile kernel of bed_scan.cuh for the plain link scan (A/B measurements)
+static bool use_tile_scanner()
+{
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("SALSA_TILE_SCANNER");
+        v = (e && *e && *e != '0') ? 1 : 0;
+    }
+    return v == 1;
+}
+
+template <bool SPARSE>
+static int scan_links(const LinkArgs &L, salsa_ctx *ctx, const void *d_bed, size_t nbytes, uint64_t base_offset, uint64_t *d_stats,
+                      cudaStream_t st)
+{
+    if (ctx->t.navoid > 0)
+        return bedscan::launch_scan<LinkPolicy<SPARSE, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
+    if (use_tile_scanner())
+        return bedscan::launch_scan<LinkPolicy<SPARSE, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
+    return bedstream::launch_stream<LinkEmit<SPARSE>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
+}
+
 __global__ void stats_reset_kernel(uint64_t *s)
 {
     s[0] = ~0ull;
@@ -138,9 +173,7 @@ extern "C" int salsa_bed_ingest_dense(salsa_ctx *ctx, const void *d_bed, size_t 
     int rc = check_ingest_args(ctx, d_bed, nbytes, d_table, d_stats);
     if (rc) return rc;
     LinkArgs L{d_table, NULL, 0};
-    if (ctx->t.navoid > 0)
-        return bedscan::launch_scan<LinkPolicy<false, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
-    return bedscan::launch_scan<LinkPolicy<false, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
+    return scan_links<false>(L, ctx, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
 }
 
 extern "C" int salsa_sparse_reset(uint64_t *d_keys, uint64_t *d_counts, size_t capacity, void *stream)
@@ -161,9 +194,7 @@ extern "C" int salsa_bed_ingest_sparse(salsa_ctx *ctx, const void *d_bed, size_t
     if (!d_keys || capacity == 0 || (capacity & (capacity - 1)))
         SALSA_FAIL(SALSA_ERR_ARG, "salsa_bed_ingest_sparse: capacity must be a power of two");
     LinkArgs L{d_counts, d_keys, capacity - 1};
-    if (ctx->t.navoid > 0)
-        return bedscan::launch_scan<LinkPolicy<true, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
-    return bedscan::launch_scan<LinkPolicy<true, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
+    return scan_links<true>(L, ctx, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
 }
 
 // Host-resident BED: chunked H2D copies overlapped with the kernel.  Chunks
@@ -204,7 +235,7 @@ extern "C" int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, si
         CUDA_TRY(cudaMemcpyAsync(dst, h + pos, end - pos, cudaMemcpyHostToDevice, ctx->s_copy));
         CUDA_TRY(cudaEventRecord(ctx->ev_copy[k & 1], ctx->s_copy));
         CUDA_TRY(cudaStreamWaitEvent(ctx->s_comp, ctx->ev_copy[k & 1], 0));
-        rc = bedscan::launch_scan<LinkPolicy<false, false>>(L, ctx->t, dst, end - pos, pos, d_stats, ctx->s_comp);
+        rc = scan_links<false>(L, ctx, dst, end - pos, pos, d_stats, ctx->s_comp);
         if (rc) return rc;
         CUDA_TRY(cudaEventRecord(ctx->ev_comp[k & 1], ctx->s_comp));
         pos = next;

@@ -1,0 +1,716 @@
+// bed_stream.cuh -- the streaming BED scanner of the link histogram (make_links.py:60-146).
+//
+// Where bed_scan.cuh cuts the text into tiles that CTAs pick up one by one, this kernel is
+// PERSISTENT and WARP-AUTONOMOUS: the buffer is cut into as many contiguous byte streams as there
+// are resident warps, and every warp walks its stream from start to end through a private ring in
+// shared memory that it fills itself with 1-D TMA bulk copies (cp.async.bulk + mbarrier, a few
+// stages ahead).  There is no block-wide barrier, no halo that is classified twice, no per-tile
+// prologue, and the "previous line" simply travels along the stream.
+//
+// Per warp, three interleaved activities:
+//   CLASSIFY  1 KiB per iteration (32 B per lane): exact SWAR byte tests + dp4a bit packing give
+//             the "special" bitmap (<= 0x20 or '/', one bit per ring byte) and the newline mask;
+//             line starts are ranked by ballot and appended to a small ring of line starts.
+//   PHASE 1   32 lines per step, one lane per line: the four field boundaries from the special
+//             bitmap, separator bytes checked, the contig name as a masked 16-byte window, the
+//             last four bytes of read.split('/')[0].  A pair of plain lines whose names are equal
+//             or whose read names provably differ is dropped here (exactly the pairs the
+//             reference neither counts nor dies on); everything else is queued.
+//   PHASE 2   16 queued pairs at a time, two lanes per pair (one line each): name -> id through
+//             the device hash table, start/end by dp4a digit conversion, full read-name compare,
+//             then the reference's checks in the reference's order and one RED into the table.
+//             A line that is not of the plain form is parsed by the byte-loop parser straight
+//             from global memory (str.split() in full): identical results, only slower.
+#pragma once
+#include "bed_scan.cuh"
+
+namespace bedstream {
+using namespace bedscan;
+
+#ifndef SALSA_STREAM_RING
+#define SALSA_STREAM_RING 8192
+#endif
+#ifndef SALSA_STREAM_WARPS
+#define SALSA_STREAM_WARPS 19
+#endif
+constexpr int RING = SALSA_STREAM_RING;     // bytes of text a warp keeps in shared memory
+constexpr int STAGE = 2048;                 // bytes per bulk copy
+constexpr int NST = RING / STAGE;
+constexpr int MIRROR = 256;                 // the ring's first bytes repeated behind its end: reads never wrap
+constexpr int FRONT = 16;                   // addressable bytes before the ring (masked-off window bytes)
+constexpr int OVER = 160;                   // phase 1 looks at a line once this much behind its start is classified
+constexpr int LCAP = 256;                   // ring of line starts (entries)
+constexpr int QCAP = 64;                    // ring of queued pairs (entries of 16 bytes)
+constexpr int QPAIRS = 16;                  // pairs per phase-2 batch (two lanes each)
+constexpr int WARPS = SALSA_STREAM_WARPS;   // warps per CTA (they share nothing but the mask table)
+constexpr int SPW = (RING + MIRROR) / 32 + 4;
+constexpr uint32_t CHUNK_MIN = 16384;       // shortest chunk worth a warp
+#ifndef SALSA_STREAM_CHUNK
+#define SALSA_STREAM_CHUNK 131072
+#endif
+constexpr uint32_t CHUNK_MAX = SALSA_STREAM_CHUNK;   // bytes of text a warp walks through before it takes the next chunk
+static_assert(RING % STAGE == 0 && NST >= 3 && (RING & (RING - 1)) == 0 && RING <= 32768, "ring geometry");
+
+constexpr size_t WARP_SMEM = FRONT + RING + MIRROR + SPW * 4 + LCAP * 4 + QCAP * 16 + NST * 8;
+static_assert(WARP_SMEM % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
+constexpr size_t CTA_SMEM = 17 * 16 + WARPS * WARP_SMEM;
+
+// ---- what phase 2 knows about one line ----
+// info bits: 0-2 nf, 3 numbad, 4 toolong, 5 has_len, 6 has_re, 7 len == 0, 8 end is 'E', 9 parsed from global memory
+struct LineInfo {
+    int id;
+    uint32_t info;
+    unsigned long long noff, roff;      // abase coordinates of the contig name and of the read token
+    uint32_t nlen, rlen;                // name length, length of read.split('/')[0]
+};
+
+__device__ __forceinline__ uint32_t gbyte(const ScanArgs &A, unsigned long long q, unsigned long long lim)
+{
+    return q < lim ? (uint32_t)__ldg(A.abase + q) : 10u;
+}
+
+// str.split() on the line that starts at abase coordinate st, read from global memory (make_links.py:62,70).
+// The first four fields must end within SALSA_MAX_LINE bytes of the line's start (library limit).
+static __device__ __noinline__ void parse_global(const ScanArgs &A, unsigned long long st, LineInfo &L, long long &sum)
+{
+    unsigned long long lim = st + SALSA_MAX_LINE;
+    const bool capped = lim < A.dend;
+    if (!capped) lim = A.dend;
+    unsigned long long p = st;
+    L.id = -1; L.info = 1u << 9; L.noff = L.roff = 0; L.nlen = L.rlen = 0;
+    sum = 0;
+    uint32_t c = gbyte(A, p, lim);
+    while (c != '\n' && is_ws(c)) c = gbyte(A, ++p, lim);
+    uint32_t nf = 0, bad = 0;
+    if (c != '\n') {
+        unsigned long long noff = p;
+        do { c = gbyte(A, ++p, lim); } while (!is_ws(c));
+        uint32_t nlen = (uint32_t)(p - noff);
+        L.noff = noff; L.nlen = nlen;
+        uint32_t w[4] = {0, 0, 0, 0};
+        for (uint32_t i = 0; i < nlen && i < 16; i++) w[i >> 2] |= (uint32_t)__ldg(A.abase + noff + i) << (8 * (i & 3));
+        {
+            const DevTable &t = A.t;
+            uint32_t h = salsa_name_hash(w[0], w[1], w[2], w[3], nlen) & t.mask;
+            for (;;) {
+                const uint4 *sp = reinterpret_cast<const uint4 *>(&t.slots[h]);
+                uint4 k = __ldg(sp), m = __ldg(sp + 1);
+                if (m.x == 0xFFFFFFFFu) break;
+                if (m.x == nlen && k.x == w[0] && k.y == w[1] && k.z == w[2] && k.w == w[3]) {
+                    bool eq = true;
+                    for (uint32_t i = 16; i < nlen; i++)
+                        if ((uint8_t)__ldg(&t.blob[m.z + i]) != __ldg(A.abase + noff + i)) { eq = false; break; }
+                    if (eq) { L.id = (int)m.y; break; }
+                }
+                h = (h + 1) & t.mask;
+            }
+        }
+        nf = 1;
+        long long val[2] = {0, 0};
+#pragma unroll
+        for (int f = 0; f < 2; f++) {
+            if (nf == 1u + f) {
+                while (c != '\n' && is_ws(c)) c = gbyte(A, ++p, lim);
+                if (c != '\n') {
+                    nf++;
+                    bool neg = (c == '-');
+                    if (c == '-' || c == '+') c = gbyte(A, ++p, lim);
+                    unsigned long long v = 0;
+                    int nd = 0;
+                    uint32_t d = c - '0';
+                    while (d <= 9u) { v = v * 10ull + d; nd++; c = gbyte(A, ++p, lim); d = c - '0'; }
+                    if (nd == 0 || nd > 18 || !is_ws(c)) bad = 8u;
+                    while (!is_ws(c)) c = gbyte(A, ++p, lim);
+                    val[f] = neg ? -(long long)v : (long long)v;
+                }
+            }
+        }
+        sum = val[0] + val[1];
+        if (nf == 3) {
+            while (c != '\n' && is_ws(c)) c = gbyte(A, ++p, lim);
+            if (c != '\n') {
+                nf = 4;
+                unsigned long long roff = p;
+                while (c != '/' && !is_ws(c)) c = gbyte(A, ++p, lim);      // read.split('/')[0]
+                L.roff = roff; L.rlen = (uint32_t)(p - roff);
+            }
+        }
+    }
+    L.info |= nf | bad | ((capped && p >= lim) ? 16u : 0u);
+}
+
+__device__ __forceinline__ bool gbytes_equal(const ScanArgs &A, unsigned long long a, unsigned long long b, uint32_t n)
+{
+    for (uint32_t i = 0; i < n; i++)
+        if (__ldg(A.abase + a + i) != __ldg(A.abase + b + i)) return false;
+    return true;
+}
+
+// ---- phase 1: the field layout of one line ----
+// P = p1 | p2 << 8 | p3 << 16 | rl << 24 (offsets of the first three separators from the line's start, length of the
+// read prefix); 0 = the line is not provably of the plain form  name SEP digits SEP digits SEP read[/...]  with
+// single tab/space separators, a name of at most 31 and a read prefix of at most ~35 bytes.  w0..w3 = the name's first
+// 16 bytes, zero padded (plain names hold no byte <= 0x20, so equal windows <=> equal names up to 16 bytes);
+// d = the last four bytes of the read prefix (whatever precedes it when it is shorter).
+struct Shp {
+    uint32_t w0, w1, w2, w3, P, d;
+};
+struct FullStep { static constexpr bool value = true; };
+struct PartStep { static constexpr bool value = false; };
+
+__device__ __forceinline__ Shp shape_of(const uint8_t *s, const uint32_t *spw, const uint4 *LM, uint32_t p, uint32_t room)
+{
+    Shp h;
+    const uint32_t i = p >> 5, sh = p & 31u;
+    const uint32_t a0 = spw[i], a1 = spw[i + 1], a2 = spw[i + 2];
+    uint32_t m0 = __funnelshift_r(a0, a1, sh), m1 = __funnelshift_r(a1, a2, sh);
+    // every step: distance to the next special byte, then shift it out (a distance of 32 = none in reach)
+    const uint32_t d1 = __clz(__brev(m0));
+    m0 = __funnelshift_rc(m0, m1, d1 + 1u); m1 = __funnelshift_rc(m1, 0u, d1 + 1u);
+    const uint32_t d2 = __clz(__brev(m0));
+    m0 = __funnelshift_rc(m0, m1, d2 + 1u); m1 = __funnelshift_rc(m1, 0u, d2 + 1u);
+    const uint32_t d3 = __clz(__brev(m0));
+    m0 = __funnelshift_rc(m0, m1, d3 + 1u); m1 = __funnelshift_rc(m1, 0u, d3 + 1u);
+    const uint32_t d4 = m0 ? __clz(__brev(m0)) : 32u + __clz(__brev(m1));
+    const uint32_t p1 = d1, p2 = p1 + 1u + d2, p3 = p2 + 1u + d3, p4 = p3 + 1u + d4;
+    const uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
+    // no short-circuit: every lane runs the same few instructions
+    const bool ok = ((((d1 | d2 | d3) & 32u) | (d4 & 64u)) == 0u) & ((d1 * d2) * (d3 * d4) != 0u) & (p4 < room) &
+                    ((c1 == 9u) | (c1 == 32u)) & ((c2 == 9u) | (c2 == 32u)) & ((c3 == 9u) | (c3 == 32u)) &
+                    ((c4 == 47u) | (c4 == 9u) | (c4 == 32u) | (c4 == 10u));
+    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(s);
+    const uint32_t a = p >> 2, shn = (p & 3u) * 8u;
+    const uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2], x3 = s32[a + 3], x4 = s32[a + 4];
+    const uint4 mk = LM[p1 > 16u ? 16u : p1];
+    h.w0 = __funnelshift_r(x0, x1, shn) & mk.x;
+    h.w1 = __funnelshift_r(x1, x2, shn) & mk.y;
+    h.w2 = __funnelshift_r(x2, x3, shn) & mk.z;
+    h.w3 = __funnelshift_r(x3, x4, shn) & mk.w;
+    const int q = (int)(p + p4) - 4;                     // p4 >= 7 on a plain line; >= -1 always (FRONT pad)
+    const uint32_t y0 = s32[q >> 2], y1 = s32[(q >> 2) + 1];
+    h.d = __funnelshift_r(y0, y1, ((uint32_t)q & 3u) * 8u);
+    h.P = ok ? (p1 | (p2 << 8) | (p3 << 16) | (d4 << 24)) : 0u;
+    return h;
+}
+
+// the n (1..12) decimal digits that END just before ring offset b -> value; false if a byte is not a digit
+__device__ __forceinline__ bool ring_digits12(const uint8_t *s, const uint4 *LM, uint32_t b, uint32_t n, long long &val)
+{
+    const uint32_t *s32 = reinterpret_cast<const uint32_t *>(s);
+    const int q = (int)b - 12;                           // >= -9: inside the FRONT pad
+    const int a = q >> 2;
+    const uint32_t sh = ((uint32_t)q & 3u) * 8u;
+    const uint32_t x0 = s32[a], x1 = s32[a + 1], x2 = s32[a + 2], x3 = s32[a + 3];
+    const uint4 mk = LM[12u - n];                        // the low 12 - n bytes of the window precede the field
+    const uint32_t u0 = (__funnelshift_r(x0, x1, sh) ^ 0x30303030u) & ~mk.x;
+    const uint32_t u1 = (__funnelshift_r(x1, x2, sh) ^ 0x30303030u) & ~mk.y;
+    const uint32_t u2 = (__funnelshift_r(x2, x3, sh) ^ 0x30303030u) & ~mk.z;
+    const uint32_t bad = ((((u0 & 0x7F7F7F7Fu) + 0x76767676u) | u0) | (((u1 & 0x7F7F7F7Fu) + 0x76767676u) | u1) |
+                          (((u2 & 0x7F7F7F7Fu) + 0x76767676u) | u2)) & 0x80808080u;
+    const uint32_t v0 = __dp4a(u0, 0x0000010Au, 0u) * 100u + __dp4a(u0, 0x010A0000u, 0u);
+    const uint32_t v1 = __dp4a(u1, 0x0000010Au, 0u) * 100u + __dp4a(u1, 0x010A0000u, 0u);
+    const uint32_t v2 = __dp4a(u2, 0x0000010Au, 0u) * 100u + __dp4a(u2, 0x010A0000u, 0u);
+    val = (long long)((unsigned long long)(v0 * 10000u + v1) * 10000ull + v2);
+    return bad == 0u;
+}
+
+__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity)
+{
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x2000;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return done;
+}
+
+// one aligned 32-bit word of the text in global memory (L2: the bytes went through it moments ago)
+__device__ __forceinline__ uint32_t gword(const uint8_t *g, unsigned long long off)
+{
+    return __ldg(reinterpret_cast<const uint32_t *>(g + (off & ~3ull)));
+}
+
+// the n (1..12) decimal digits that END just before global offset b (b >= 16)
+__device__ __forceinline__ bool global_digits12(const uint8_t *g, const uint4 *LM, unsigned long long b, uint32_t n, long long &val)
+{
+    const unsigned long long q = b - 12ull;
+    const uint32_t sh = ((uint32_t)q & 3u) * 8u;
+    const uint32_t x0 = gword(g, q), x1 = gword(g, q + 4), x2 = gword(g, q + 8), x3 = gword(g, q + 12);
+    const uint4 mk = LM[12u - n];                        // the low 12 - n bytes of the window precede the field
+    const uint32_t u0 = (__funnelshift_r(x0, x1, sh) ^ 0x30303030u) & ~mk.x;
+    const uint32_t u1 = (__funnelshift_r(x1, x2, sh) ^ 0x30303030u) & ~mk.y;
+    const uint32_t u2 = (__funnelshift_r(x2, x3, sh) ^ 0x30303030u) & ~mk.z;
+    const uint32_t bad = ((((u0 & 0x7F7F7F7Fu) + 0x76767676u) | u0) | (((u1 & 0x7F7F7F7Fu) + 0x76767676u) | u1) |
+                          (((u2 & 0x7F7F7F7Fu) + 0x76767676u) | u2)) & 0x80808080u;
+    const uint32_t v0 = __dp4a(u0, 0x0000010Au, 0u) * 100u + __dp4a(u0, 0x010A0000u, 0u);
+    const uint32_t v1 = __dp4a(u1, 0x0000010Au, 0u) * 100u + __dp4a(u1, 0x010A0000u, 0u);
+    const uint32_t v2 = __dp4a(u2, 0x0000010Au, 0u) * 100u + __dp4a(u2, 0x010A0000u, 0u);
+    val = (long long)((unsigned long long)(v0 * 10000u + v1) * 10000ull + v2);
+    return bad == 0u;
+}
+
+// name (first 16 bytes in w0..w3, the rest in global memory at noff + 16 ...) -> contig id or -1
+__device__ __forceinline__ int lookup_global(const DevTable &t, const uint8_t *g, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3,
+                                             unsigned long long noff, uint32_t nlen, uint32_t h)
+{
+    for (;;) {
+        const uint4 *sp = reinterpret_cast<const uint4 *>(&t.slots[h]);
+        const uint4 k = __ldg(sp), m = __ldg(sp + 1);     // words; len, id, blob_off, pad
+        if (m.x == 0xFFFFFFFFu) return -1;
+        if (m.x == nlen && k.x == w0 && k.y == w1 && k.z == w2 && k.w == w3) {
+            bool eq = true;
+            for (uint32_t i = 16; i < nlen; i++)
+                if ((uint8_t)__ldg(&t.blob[m.z + i]) != __ldg(g + noff + i)) { eq = false; break; }
+            if (eq) return (int)m.y;
+        }
+        h = (h + 1) & t.mask;
+    }
+}
+
+template <class Emit>
+__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t chunk_bytes, uint32_t nchunks)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint4 *LM = reinterpret_cast<uint4 *>(smem);          // LM[e]: the low e bytes of a 16-byte window
+    if (threadIdx.x < 17) {
+        uint32_t m[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            int nbv = (int)threadIdx.x - 4 * j;
+            m[j] = nbv >= 4 ? 0xFFFFFFFFu : (nbv <= 0 ? 0u : ((1u << (8 * nbv)) - 1u));
+        }
+        LM[threadIdx.x] = make_uint4(m[0], m[1], m[2], m[3]);
+    }
+    uint8_t *base = smem + 17 * 16 + (size_t)warp * WARP_SMEM;
+    uint8_t *s = base + FRONT;                                                  // the ring
+    uint32_t *spw = reinterpret_cast<uint32_t *>(s + RING + MIRROR);            // special bitmap, bit per ring byte
+    uint32_t *lines = spw + SPW;                                                // ring of line starts (stream offsets)
+    uint4 *queue = reinterpret_cast<uint4 *>(lines + LCAP);                     // (cur start, prev start, P cur, P prev)
+    const uint32_t bar0 = smem_u32(queue + QCAP);                               // NST mbarriers
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NST; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * i));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (lane < 4) reinterpret_cast<uint32_t *>(base)[lane] = 0u;
+    __syncthreads();                                                            // the mask table; the only block-wide barrier
+
+    uint32_t nlines = 0, npairs = 0;
+    const unsigned ltmask = (1u << lane) - 1u;
+    const unsigned long long dend = A.dend, dend16 = (dend + 15ull) & ~15ull;
+    // Chunks are dealt round robin: at any time the warps of the whole GPU work side by side in one window of the text
+    // (a few hundred MB), which keeps the TLB and the DRAM pages they touch few.
+    for (uint32_t ck = blockIdx.x * WARPS + warp; ck < nchunks; ck += gridDim.x * WARPS) {
+    // ---- the chunk, in abase coordinates ----
+    const unsigned long long S0 = (unsigned long long)ck * chunk_bytes;
+    unsigned long long S1 = S0 + chunk_bytes;
+    if (S1 > dend || ck + 1 == nchunks) S1 = dend;
+    const unsigned long long lo = S0 >= (unsigned long long)HALO ? S0 - HALO : 0ull;      // first byte loaded
+    unsigned long long hi = S1 + HALO;                                                    // one past the last byte classified
+    const bool at_end = hi >= dend16;
+    if (at_end) hi = dend16;
+    const uint8_t *gsrc = A.abase + lo;
+    // ---- the same, relative to lo (32 bit) ----
+    const uint32_t rel_end = (uint32_t)(hi - lo);
+    const uint32_t dend_rel = at_end ? (uint32_t)(dend - lo) : 0xFFFFFF00u;
+    const uint32_t lim = at_end ? dend_rel + 1u : rel_end;             // a plain line's fourth separator lies below this
+    const uint32_t own_lo = lo == 0 ? A.mis : (uint32_t)(S0 - lo);     // lines that start beyond it are this chunk's
+    const uint32_t nl_lo = lo == 0 ? A.mis : 0u;                       // newlines q in [nl_lo, nl_hi) open a line we look at
+    const unsigned long long nlh = S1 < dend - 1 ? S1 : dend - 1;
+    const uint32_t nl_hi = (uint32_t)(nlh - lo);
+    const uint32_t nst = (rel_end + STAGE - 1) / STAGE;
+    const uint32_t sent_stage = at_end ? nst - 1u : 0xFFFFFFFFu;        // the stage behind which the sentinel goes
+    const uint32_t wr_end = at_end ? rel_end + 64u : rel_end;          // bitmap words are written up to here (sentinel included)
+    const uint64_t file_base = A.base_offset - (uint64_t)A.mis + lo;    // file offset of chunk offset 0
+    // phase 2 reads a plain line's words from global memory: keep clear of both ends of the buffer
+    const uint32_t g_lo = lo >= 16ull ? 0u : 16u - (uint32_t)lo;
+    const uint32_t g_hi = !at_end ? 0xFFFFFF00u : (dend_rel >= 192u ? dend_rel - 192u : 0u);
+
+    uint32_t cpos = 0, lh = 0, lt = 0, qh = 0, qn = 0, issued = 0, ready = 0;   // ready: bytes of the chunk that have arrived
+    uint32_t cls_lim = 0;                // classification may run while cpos + 1024 <= cls_lim
+    uint32_t over_eff = OVER;            // a line is looked at once this much text behind its start is classified (0 at the end)
+    uint32_t next_need = 0;              // the next stage can be issued once low has reached this
+    Shp hp;                              // the shapes of the previous step (lane 31's is the next step's "previous")
+    hp.w0 = hp.w1 = hp.w2 = hp.w3 = hp.P = hp.d = 0;
+    uint32_t hp_start = 0;
+    uint32_t low = 0;                    // ring bytes from here on are still needed (start of the last line looked at)
+    bool have_prev = false;
+
+    if (lo == 0) {                      // the buffer's first line: it only ever plays "previous" (make_links.py:66-68)
+        if (lane == 0) lines[0] = A.mis;
+        lt = 1;
+    }
+    __syncwarp();
+
+    // ---- bulk copies: as many stages as the ring has room for ----
+    auto issue_allowed = [&]() {
+        // stage t overwrites what stage t - NST held; the last stage also needs room for the sentinel behind it
+        while (issued < nst) {
+            const uint32_t tt = issued + (issued == sent_stage ? 2u : 1u);
+            next_need = tt >= (uint32_t)NST ? (tt - NST) * STAGE : 0u;
+            if (low < next_need) return;
+            const uint32_t slot = issued % NST, off = issued * STAGE;
+            const uint32_t nb = rel_end - off < (uint32_t)STAGE ? rel_end - off : (uint32_t)STAGE;
+            const uint32_t mir = slot == 0 ? (nb < (uint32_t)MIRROR ? nb : (uint32_t)MIRROR) : 0u;
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t b = bar0 + 8u * slot;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(nb + mir) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                 smem_u32(s + slot * STAGE)),
+                             "l"(gsrc + off), "r"(nb), "r"(b)
+                             : "memory");
+                if (mir)
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                     smem_u32(s + RING)),
+                                 "l"(gsrc + off), "r"(mir), "r"(b)
+                                 : "memory");
+            }
+            issued++;
+        }
+        next_need = 0xFFFFFFFFu;
+    };
+    auto wait_next = [&]() {                      // the next stage has been issued: wait for it (every lane observes the phase itself)
+        const uint32_t t = ready / STAGE;
+        const uint32_t b = bar0 + 8u * (t % NST), par = (t / NST) & 1u;
+        while (!mbar_try(b, par)) {}
+        if (t == sent_stage) {                    // sentinel: the data ends like a line ends
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                uint32_t o = (dend_rel + (uint32_t)lane * 2u + j) & (RING - 1);
+                s[o] = '\n';
+                if (o < (uint32_t)MIRROR) s[RING + o] = '\n';
+            }
+            __syncwarp();
+        }
+        ready += STAGE;
+        cls_lim = ready >= rel_end ? rel_end + 1023u : ready;
+    };
+
+    // ---- phase 2: nb (<= 16) queued pairs, two lanes per pair ----
+    auto flush = [&](uint32_t nb) {
+        const uint32_t ei = (uint32_t)lane >> 1, role = (uint32_t)lane & 1u;    // role 0: the pair's current line, 1: its previous line
+        const bool act = ei < nb;
+        uint4 e = make_uint4(0, 0, 0, 0);
+        if (act) e = queue[(qh + ei) & (QCAP - 1)];
+        const uint32_t st = role ? e.y : e.x, P = role ? e.w : e.z;
+        LineInfo L;
+        L.id = -1; L.info = 0; L.noff = L.roff = 0; L.nlen = L.rlen = 0;
+        long long sum = 0;
+        const uint32_t p1 = P & 255u, p2 = (P >> 8) & 255u, p3 = (P >> 16) & 255u, rl = P >> 24;
+        const uint32_t n1 = p2 - p1 - 1u, n2 = p3 - p2 - 1u;
+        bool slow = act;
+        if (act && P != 0u && st >= g_lo && st <= g_hi && n1 <= 12u && n2 <= 12u) {
+            const unsigned long long g = (unsigned long long)st;      // offset from gsrc
+            const uint32_t shn = (st & 3u) * 8u;
+            const uint32_t x0 = gword(gsrc, g), x1 = gword(gsrc, g + 4), x2 = gword(gsrc, g + 8), x3 = gword(gsrc, g + 12),
+                           x4 = gword(gsrc, g + 16);
+            const uint4 mk = LM[p1 > 16u ? 16u : p1];
+            const uint32_t w0 = __funnelshift_r(x0, x1, shn) & mk.x, w1 = __funnelshift_r(x1, x2, shn) & mk.y;
+            const uint32_t w2 = __funnelshift_r(x2, x3, shn) & mk.z, w3 = __funnelshift_r(x3, x4, shn) & mk.w;
+            // the first probe's latency hides behind the digit conversion
+            const uint32_t hsh = salsa_name_hash(w0, w1, w2, w3, p1) & A.t.mask;
+            const uint4 *slot = reinterpret_cast<const uint4 *>(&A.t.slots[hsh]);
+            const uint4 k0 = __ldg(slot), m0 = __ldg(slot + 1);
+            long long vs, ve;
+            const bool dg1 = global_digits12(gsrc, LM, g + p2, n1, vs);
+            const bool dg2 = global_digits12(gsrc, LM, g + p3, n2, ve);
+            if (dg1 && dg2) {                        // else signs, junk: the full parser classifies it
+                sum = vs + ve;
+                if (p1 <= 16u && m0.x == p1 && k0.x == w0 && k0.y == w1 && k0.z == w2 && k0.w == w3) L.id = (int)m0.y;
+                else if (p1 <= 16u && m0.x == 0xFFFFFFFFu) L.id = -1;
+                else L.id = lookup_global(A.t, gsrc, w0, w1, w2, w3, g, p1, hsh);
+                L.info = 4u;
+                L.noff = lo + st; L.nlen = p1;
+                L.roff = lo + st + p3 + 1u; L.rlen = rl;
+                slow = false;
+            }
+        }
+        if (slow) {                                  // results through local memory only on this path
+            LineInfo T;
+            long long tsum;
+            parse_global(A, lo + st, T, tsum);
+            L = T;
+            sum = tsum;
+        }
+        if (L.id >= 0) {
+            const ContigMeta m = A.t.meta[L.id];
+            L.info |= ((m.flags & SALSA_CTG_HAS_LEN) ? 32u : 0u) | ((m.flags & SALSA_CTG_HAS_RE) ? 64u : 0u) |
+                      (m.len_floor == 0 ? 128u : 0u) | (sum > m.len_floor ? 256u : 0u);
+        }
+        // ---- read.split('/')[0] of both lines (make_links.py:78) ----
+        const uint32_t oinfo = __shfl_xor_sync(0xffffffffu, L.info, 1);
+        const int oid = __shfl_xor_sync(0xffffffffu, L.id, 1);
+        const uint32_t orl = __shfl_xor_sync(0xffffffffu, L.rlen, 1);
+        const bool pslow = ((L.info | oinfo) & 512u) != 0u;     // one of the pair's lines came through the full parser
+        bool req;
+        {
+            // both lines plain: word by word, each lane its own line
+            const unsigned long long r0 = (unsigned long long)st + p3 + 1u;
+            const uint32_t nw = (act && !pslow) ? (rl + 3u) >> 2 : 0u;
+            const uint32_t nwmax = __reduce_max_sync(0xffffffffu, nw);
+            uint32_t diff = L.rlen ^ orl;
+            for (uint32_t j = 0; j < nwmax; j++) {
+                uint32_t w = 0;
+                if (j < nw) {
+                    const unsigned long long q = r0 + 4u * j;
+                    w = __funnelshift_r(gword(gsrc, q), gword(gsrc, q + 4), ((uint32_t)q & 3u) * 8u);
+                    const uint32_t left = rl - 4u * j;
+                    if (left < 4u) w &= (1u << (8u * left)) - 1u;
+                }
+                diff |= w ^ __shfl_xor_sync(0xffffffffu, w, 1);
+            }
+            req = diff == 0u;
+        }
+        bool same_name = false;
+        if (__any_sync(0xffffffffu, act && (pslow || (L.id < 0 && oid < 0)))) {
+            // rare: compare byte by byte in global memory (a line from the full parser, or two unknown names)
+            const unsigned long long oroff = __shfl_xor_sync(0xffffffffu, L.roff, 1), onoff = __shfl_xor_sync(0xffffffffu, L.noff, 1);
+            const uint32_t onlen = __shfl_xor_sync(0xffffffffu, L.nlen, 1);
+            if (act && !role) {
+                if (pslow) req = L.rlen == orl && gbytes_equal(A, L.roff, oroff, orl);
+                if (L.id < 0 && oid < 0) same_name = L.nlen == onlen && gbytes_equal(A, L.noff, onoff, onlen);
+            }
+        }
+        // ---- the reference's body for one adjacent-line pair, in its order (make_links.py:70-144) ----
+        if (act && !role) {
+            const uint64_t line_off = file_base + e.x;
+            const uint32_t cnf = L.info & 7u, pnf = oinfo & 7u, both = L.info | oinfo, all = L.info & oinfo;
+            const bool same = (L.id >= 0 && oid >= 0) ? L.id == oid : ((L.id ^ oid) < 0 ? false : same_name);
+            if (both & 16u) report(A.stats, line_off, SALSA_DATA_LINE_TOO_LONG);
+            else if (pnf < 1u || cnf < 1u) report(A.stats, line_off, SALSA_DATA_INDEX_ERROR);                // :71
+            else if (same) {}
+            else if (pnf < 4u || cnf < 4u) report(A.stats, line_off, SALSA_DATA_INDEX_ERROR);                // :76-77
+            else if (!req) {}                                                                                 // :78
+            else if (both & 8u) report(A.stats, line_off, SALSA_DATA_VALUE_ERROR);                            // :81-82
+            else if (L.id < 0 || oid < 0) report(A.stats, line_off, SALSA_DATA_KEY_ERROR);                    // :101-102
+            else if (!(all & 32u)) report(A.stats, line_off, SALSA_DATA_KEY_ERROR);
+            else if (both & 128u) report(A.stats, line_off, SALSA_DATA_ZERO_DIV);                             // :106-107
+            else if (!(all & 64u)) report(A.stats, line_off, SALSA_DATA_KEY_ERROR);                           // :113
+            else {
+                // B <=> pos <= len/2 <=> start+end <= floor(len); E otherwise (:108-139); names ordered as strings (:90-96)
+                const uint32_t ec = (L.info >> 8) & 1u, ep = (oinfo >> 8) & 1u;
+                uint32_t first, second, ends;
+                if (oid < L.id) { first = (uint32_t)oid; second = (uint32_t)L.id; ends = ep * 2u + ec; }
+                else { first = (uint32_t)L.id; second = (uint32_t)oid; ends = ec * 2u + ep; }
+                const uint64_t key = (((uint64_t)first * (uint64_t)A.t.n + second) << 2) | ends;
+                Emit::emit(EA, A, key, line_off);
+                npairs++;
+            }
+        }
+        qh += nb;
+        qn -= nb;
+        __syncwarp();
+    };
+
+    // ---- phase 1: nv (1..32) lines, entries lh .. lh + nv - 1 of the ring of line starts ----
+    auto step = [&](uint32_t nv, auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        const bool actv = FULL || (uint32_t)lane < nv;
+        const uint32_t start = lines[(lh + (uint32_t)lane) & (LCAP - 1)];
+        Shp h;
+        h.w0 = h.w1 = h.w2 = h.w3 = h.P = h.d = 0;
+        if (actv) h = shape_of(s, spw, LM, start & (RING - 1), lim - start);
+        // the line before: lane - 1's, and for lane 0 lane 31's of the step before (one rotation does both)
+        const bool l31 = lane == 31;
+        const int src = (lane + 31) & 31;
+        Shp ph;
+        ph.w0 = __shfl_sync(0xffffffffu, l31 ? hp.w0 : h.w0, src); ph.w1 = __shfl_sync(0xffffffffu, l31 ? hp.w1 : h.w1, src);
+        ph.w2 = __shfl_sync(0xffffffffu, l31 ? hp.w2 : h.w2, src); ph.w3 = __shfl_sync(0xffffffffu, l31 ? hp.w3 : h.w3, src);
+        ph.P = __shfl_sync(0xffffffffu, l31 ? hp.P : h.P, src); ph.d = __shfl_sync(0xffffffffu, l31 ? hp.d : h.d, src);
+        const uint32_t pstart = __shfl_sync(0xffffffffu, l31 ? hp_start : start, src);
+        const bool owned = actv && start > own_lo;
+        bool cand = owned;
+        if (!have_prev && lane == 0) {
+            // a stream's first line start is known to be one only behind a newline of the halo
+            if (owned) report(A.stats, file_base + start, SALSA_DATA_LINE_TOO_LONG);
+            cand = false;
+        }
+        if (h.P != 0u && ph.P != 0u) {
+            bool same = ((h.w0 ^ ph.w0) | (h.w1 ^ ph.w1) | (h.w2 ^ ph.w2) | (h.w3 ^ ph.w3)) == 0u;
+            const uint32_t nl = h.P & 255u, pnl = ph.P & 255u;
+            if (same && (nl | pnl) > 16u)        // a name longer than the window: the rest byte by byte (both lines are in the ring)
+                same = nl == pnl && bytes_equal_back(s, (int)((pstart & (RING - 1)) + 16u), (int)((start & (RING - 1)) + 16u), (int)nl - 16);
+            const bool rmay = ((h.P ^ ph.P) >> 24) == 0u && ((h.P >> 24) < 4u || h.d == ph.d);
+            cand = cand && !same && rmay;              // names differ and the read names may be equal
+        }
+        const unsigned om = __ballot_sync(0xffffffffu, owned);
+        const unsigned cm = __ballot_sync(0xffffffffu, cand);
+        nlines += __popc(om);
+        if (cand) queue[(qh + qn + __popc(cm & ltmask)) & (QCAP - 1)] = make_uint4(start, pstart, h.P, ph.P);
+        qn += __popc(cm);
+        hp = h;
+        hp_start = start;
+        if (!FULL && nv != 32u) {        // a short step (end of the chunk, or the ring was full): its last line goes to lane 31
+            const int last = (int)nv - 1;
+            hp.w0 = __shfl_sync(0xffffffffu, h.w0, last); hp.w1 = __shfl_sync(0xffffffffu, h.w1, last);
+            hp.w2 = __shfl_sync(0xffffffffu, h.w2, last); hp.w3 = __shfl_sync(0xffffffffu, h.w3, last);
+            hp.P = __shfl_sync(0xffffffffu, h.P, last); hp.d = __shfl_sync(0xffffffffu, h.d, last);
+            hp_start = __shfl_sync(0xffffffffu, start, last);
+        }
+        low = __shfl_sync(0xffffffffu, hp_start, 31);
+        have_prev = true;
+        lh += FULL ? 32u : nv;
+        __syncwarp();
+    };
+
+    // ---- classify 1 KiB from cpos on: special bitmap + line starts ----
+    auto classify = [&]() {
+        const uint32_t c = cpos + 32u * (uint32_t)lane;
+        const uint32_t ro = c & (RING - 1);
+        const uint4 v0 = *reinterpret_cast<const uint4 *>(s + ro), v1 = *reinterpret_cast<const uint4 *>(s + ro + 16);
+        uint32_t m32 = nl16_of(v0) | (nl16_of(v1) << 16);
+        const uint32_t sp = sp16_of(v0) | (sp16_of(v1) << 16);
+        if (cpos >= nl_lo && cpos + 1024u <= nl_hi) {      // everywhere but in the stream's first and last iterations
+            spw[ro >> 5] = sp;
+            if (ro < (uint32_t)MIRROR) spw[(RING + ro) >> 5] = sp;
+        } else {
+            if (c < wr_end) {                              // beyond the stream the ring may hold older, live text
+                spw[ro >> 5] = sp;
+                if (ro < (uint32_t)MIRROR) spw[(RING + ro) >> 5] = sp;
+            }
+            // newlines outside [nl_lo, nl_hi) open no line of this stream
+            int a = (int)nl_lo - (int)c, b = (long long)nl_hi - (long long)c > 32 ? 32 : (int)((long long)nl_hi - (long long)c);
+            a = a < 0 ? 0 : (a > 32 ? 32 : a);
+            b = b < 0 ? 0 : b;
+            const uint32_t lowb = b >= 32 ? 0xFFFFFFFFu : ((1u << b) - 1u), lowa = a >= 32 ? 0xFFFFFFFFu : ((1u << a) - 1u);
+            m32 &= b > a ? (lowb & ~lowa) : 0u;
+        }
+        const unsigned has = __ballot_sync(0xffffffffu, m32 != 0u);
+        const unsigned multi = __ballot_sync(0xffffffffu, (m32 & (m32 - 1u)) != 0u);
+        if (multi == 0u) {                         // at most one newline per 32 bytes: rank by ballot
+            if (m32) lines[(lt + __popc(has & ltmask)) & (LCAP - 1)] = c + __ffs(m32);
+            lt += __popc(has);
+            cpos += 1024u;
+        } else {
+            // general case: inclusive scan of the counts; only the lanes whose newlines all fit the ring of line
+            // starts are consumed, the next iteration starts at the first lane that was not
+            const uint32_t room = (uint32_t)LCAP - (lt - lh);
+            int cnt = __popc(m32), inc = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            const unsigned fit = __ballot_sync(0xffffffffu, (uint32_t)inc <= room);
+            const int ncons = fit == 0xFFFFFFFFu ? 32 : __ffs(~fit) - 1;       // a prefix of the lanes (inc is monotone), >= 1
+            uint32_t pos = lt + (uint32_t)(inc - cnt);
+            if (lane < ncons) {
+                while (m32) {
+                    const int b = __ffs(m32);
+                    m32 &= m32 - 1u;
+                    lines[pos & (LCAP - 1)] = c + (uint32_t)b;
+                    pos++;
+                }
+            }
+            lt += (uint32_t)__shfl_sync(0xffffffffu, inc, ncons - 1);
+            cpos += 32u * (uint32_t)ncons;
+        }
+        __syncwarp();
+    };
+
+    // ---- the chunk ----
+    issue_allowed();
+    for (;;) {
+        const uint32_t cnt = lt - lh;
+        if (cnt >= 32u && cpos - lines[(lh + 31u) & (LCAP - 1)] >= over_eff) {
+            step(32u, FullStep());
+            while (qn >= (uint32_t)QPAIRS) flush(QPAIRS);
+            if (low >= next_need) issue_allowed();
+            continue;
+        }
+        if (cpos + 1024u <= cls_lim && cnt <= (uint32_t)LCAP - 32u) {
+            classify();
+            if (cpos >= rel_end) over_eff = 0u;
+            continue;
+        }
+        // ---- the rare paths: waiting for text, the end of the chunk, a line longer than the ring ----
+        uint32_t nv = 0;
+        if (cpos < rel_end) {
+            if (cnt <= (uint32_t)LCAP - 32u) {
+                issue_allowed();
+                if (ready < issued * STAGE) { wait_next(); continue; }
+            }
+            // no room in the ring, because of one very long line: look at what can be looked at, then let go of the line before it
+            const uint32_t vi = lines[(lh + (uint32_t)lane) & (LCAP - 1)];
+            nv = __popc(__ballot_sync(0xffffffffu, (uint32_t)lane < cnt && cpos - vi >= (uint32_t)OVER));
+            if (!nv) {
+                const uint32_t st0 = cnt ? lines[lh & (LCAP - 1)] : cpos;      // nothing older than this is needed any more
+                if (low != st0 || hp.P) { hp.P = 0u; low = st0; continue; }
+                if (lane == 0) report(A.stats, file_base + cpos, SALSA_DATA_LINE_TOO_LONG);     // cannot happen: RING >> OVER + 2 * STAGE
+                break;
+            }
+        } else if (cnt) nv = cnt;              // < 32: the chunk's last lines
+        else break;
+        step(nv, PartStep());
+        while (qn >= (uint32_t)QPAIRS) flush(QPAIRS);
+    }
+    while (qn) flush(qn < (uint32_t)QPAIRS ? qn : (uint32_t)QPAIRS);
+    // every bulk copy of this chunk has arrived; the barriers start over with the next chunk
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NST; i++) {
+            asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar0 + 8u * i) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * i) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    }   // chunks
+
+    // ---- statistics: one atomic pair per warp ----
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, d);
+    if (lane == 0) {
+        if (nlines) atomicAdd((unsigned long long *)&A.stats[1], (unsigned long long)nlines);
+        if (npairs) atomicAdd((unsigned long long *)&A.stats[2], (unsigned long long)npairs);
+    }
+}
+
+template <class Emit>
+int launch_stream(const typename Emit::Args &EA, const DevTable &t, const void *d_bed, size_t nbytes, uint64_t base_offset,
+                  uint64_t *stats, cudaStream_t st)
+{
+    if (nbytes == 0) return SALSA_OK;
+    ScanArgs A;
+    uintptr_t p = (uintptr_t)d_bed;
+    A.mis = (uint32_t)(p & 15u);
+    A.abase = (const uint8_t *)(p - A.mis);
+    A.dend = (uint64_t)A.mis + nbytes;
+    A.base_offset = base_offset;
+    A.t = t;
+    A.stats = stats;
+    static int ctas_per_dev[64] = {0};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) SALSA_FAIL(SALSA_ERR_ARG, "device index %d out of range", dev);
+    if (!ctas_per_dev[dev]) {
+        int sms = 0, per = 0;
+        CUDA_TRY(cudaFuncSetAttribute(bed_stream_kernel<Emit>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CTA_SMEM));
+        CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, bed_stream_kernel<Emit>, WARPS * 32, CTA_SMEM));
+        if (per < 1) SALSA_FAIL(SALSA_ERR_CUDA, "bed_stream_kernel does not fit an SM (%zu bytes of shared memory)", CTA_SMEM);
+        ctas_per_dev[dev] = sms * per;
+    }
+    CUDA_TRY(cudaFuncSetAttribute(bed_stream_kernel<Emit>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CTA_SMEM));
+    const uint64_t nwarps = (uint64_t)ctas_per_dev[dev] * WARPS;
+    uint64_t cb = (A.dend + nwarps - 1) / nwarps;       // every resident warp gets at least one chunk ...
+    if (cb < CHUNK_MIN) cb = CHUNK_MIN;
+    if (cb > CHUNK_MAX) cb = CHUNK_MAX;                 // ... and large inputs are dealt out in chunks of CHUNK_MAX
+    cb = (cb + 1023) & ~1023ull;                        // chunks start on 1 KiB: ring offsets, stages and iterations stay aligned
+    const uint64_t nchunks = (A.dend + cb - 1) / cb;
+    if (nchunks > 0x7fffffffull) SALSA_FAIL(SALSA_ERR_ARG, "BED chunk too large (%zu bytes)", nbytes);
+    uint64_t ctas = (nchunks + WARPS - 1) / WARPS;
+    if (ctas > (uint64_t)ctas_per_dev[dev]) ctas = (uint64_t)ctas_per_dev[dev];
+    bed_stream_kernel<Emit><<<(unsigned)ctas, WARPS * 32, CTA_SMEM, st>>>(EA, A, (uint32_t)cb, (uint32_t)nchunks);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
+}   // namespace bedstream
