@@ -31,11 +31,11 @@ using namespace bedscan;
 #define SALSA_STREAM_RING 8192
 #endif
 #ifndef SALSA_STREAM_WARPS
-#define SALSA_STREAM_WARPS 19
+#define SALSA_STREAM_WARPS 20
 #endif
 constexpr int RING = SALSA_STREAM_RING;     // bytes of text a warp keeps in shared memory
-constexpr int STAGE = 2048;                 // bytes per bulk copy
-constexpr int NST = RING / STAGE;
+constexpr int GRP = 2048;                   // bytes per cp.async group = one classification iteration (64 bytes per lane)
+constexpr int NGR = RING / GRP;
 constexpr int MIRROR = 256;                 // the ring's first bytes repeated behind its end: reads never wrap
 constexpr int FRONT = 16;                   // addressable bytes before the ring (masked-off window bytes)
 constexpr int OVER = 160;                   // phase 1 looks at a line once this much behind its start is classified
@@ -49,9 +49,9 @@ constexpr uint32_t CHUNK_MIN = 16384;       // shortest chunk worth a warp
 #define SALSA_STREAM_CHUNK 131072
 #endif
 constexpr uint32_t CHUNK_MAX = SALSA_STREAM_CHUNK;   // bytes of text a warp walks through before it takes the next chunk
-static_assert(RING % STAGE == 0 && NST >= 3 && (RING & (RING - 1)) == 0 && RING <= 32768, "ring geometry");
+static_assert(RING % GRP == 0 && NGR >= 4 && NGR <= 8 && (RING & (RING - 1)) == 0, "ring geometry");
 
-constexpr size_t WARP_SMEM = FRONT + RING + MIRROR + SPW * 4 + LCAP * 4 + QCAP * 16 + NST * 8;
+constexpr size_t WARP_SMEM = FRONT + RING + MIRROR + SPW * 4 + LCAP * 4 + QCAP * 16;
 static_assert(WARP_SMEM % 16 == 0, "per-warp shared memory must keep 16-byte alignment");
 constexpr size_t CTA_SMEM = 17 * 16 + WARPS * WARP_SMEM;
 
@@ -155,8 +155,6 @@ __device__ __forceinline__ bool gbytes_equal(const ScanArgs &A, unsigned long lo
 struct Shp {
     uint32_t w0, w1, w2, w3, P, d;
 };
-struct FullStep { static constexpr bool value = true; };
-struct PartStep { static constexpr bool value = false; };
 
 __device__ __forceinline__ Shp shape_of(const uint8_t *s, const uint32_t *spw, const uint4 *LM, uint32_t p, uint32_t room)
 {
@@ -214,23 +212,22 @@ __device__ __forceinline__ bool ring_digits12(const uint8_t *s, const uint4 *LM,
     return bad == 0u;
 }
 
-__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity)
+// cp.async.wait_group takes an immediate: wait until at most `ahead` of this thread's groups are still in flight
+__device__ __forceinline__ void wait_groups(uint32_t ahead)
 {
-    uint32_t done;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x2000;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    return done;
+    if (ahead >= 6u) asm volatile("cp.async.wait_group 6;" ::: "memory");
+    else if (ahead == 5u) asm volatile("cp.async.wait_group 5;" ::: "memory");
+    else if (ahead == 4u) asm volatile("cp.async.wait_group 4;" ::: "memory");
+    else if (ahead == 3u) asm volatile("cp.async.wait_group 3;" ::: "memory");
+    else if (ahead == 2u) asm volatile("cp.async.wait_group 2;" ::: "memory");
+    else if (ahead == 1u) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 // one aligned 32-bit word of the text in global memory (L2: the bytes went through it moments ago)
-__device__ __forceinline__ uint32_t gword(const uint8_t *g, unsigned long long off)
+__device__ __forceinline__ const uint32_t *gwords(const uint8_t *g, unsigned long long off)
 {
-    return __ldg(reinterpret_cast<const uint32_t *>(g + (off & ~3ull)));
+    return reinterpret_cast<const uint32_t *>(g + (off & ~3ull));
 }
 
 // the n (1..12) decimal digits that END just before global offset b (b >= 16)
@@ -238,7 +235,8 @@ __device__ __forceinline__ bool global_digits12(const uint8_t *g, const uint4 *L
 {
     const unsigned long long q = b - 12ull;
     const uint32_t sh = ((uint32_t)q & 3u) * 8u;
-    const uint32_t x0 = gword(g, q), x1 = gword(g, q + 4), x2 = gword(g, q + 8), x3 = gword(g, q + 12);
+    const uint32_t *gp = gwords(g, q);
+    const uint32_t x0 = __ldg(gp), x1 = __ldg(gp + 1), x2 = __ldg(gp + 2), x3 = __ldg(gp + 3);
     const uint4 mk = LM[12u - n];                        // the low 12 - n bytes of the window precede the field
     const uint32_t u0 = (__funnelshift_r(x0, x1, sh) ^ 0x30303030u) & ~mk.x;
     const uint32_t u1 = (__funnelshift_r(x1, x2, sh) ^ 0x30303030u) & ~mk.y;
@@ -290,12 +288,6 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     uint32_t *spw = reinterpret_cast<uint32_t *>(s + RING + MIRROR);            // special bitmap, bit per ring byte
     uint32_t *lines = spw + SPW;                                                // ring of line starts (stream offsets)
     uint4 *queue = reinterpret_cast<uint4 *>(lines + LCAP);                     // (cur start, prev start, P cur, P prev)
-    const uint32_t bar0 = smem_u32(queue + QCAP);                               // NST mbarriers
-    if (lane == 0) {
-#pragma unroll
-        for (int i = 0; i < NST; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * i));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
     if (lane < 4) reinterpret_cast<uint32_t *>(base)[lane] = 0u;
     __syncthreads();                                                            // the mask table; the only block-wide barrier
 
@@ -322,18 +314,25 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     const uint32_t nl_lo = lo == 0 ? A.mis : 0u;                       // newlines q in [nl_lo, nl_hi) open a line we look at
     const unsigned long long nlh = S1 < dend - 1 ? S1 : dend - 1;
     const uint32_t nl_hi = (uint32_t)(nlh - lo);
-    const uint32_t nst = (rel_end + STAGE - 1) / STAGE;
-    const uint32_t sent_stage = at_end ? nst - 1u : 0xFFFFFFFFu;        // the stage behind which the sentinel goes
+    const uint32_t ngr = (rel_end + GRP - 1) / GRP;                     // cp.async groups of this chunk
     const uint32_t wr_end = at_end ? rel_end + 64u : rel_end;          // bitmap words are written up to here (sentinel included)
     const uint64_t file_base = A.base_offset - (uint64_t)A.mis + lo;    // file offset of chunk offset 0
     // phase 2 reads a plain line's words from global memory: keep clear of both ends of the buffer
     const uint32_t g_lo = lo >= 16ull ? 0u : 16u - (uint32_t)lo;
     const uint32_t g_hi = !at_end ? 0xFFFFFF00u : (dend_rel >= 192u ? dend_rel - 192u : 0u);
 
-    uint32_t cpos = 0, lh = 0, lt = 0, qh = 0, qn = 0, issued = 0, ready = 0;   // ready: bytes of the chunk that have arrived
-    uint32_t cls_lim = 0;                // classification may run while cpos + 1024 <= cls_lim
+    // the last group (when the text ends in this chunk) needs room for the sentinel behind it and gets it written
+    uint32_t ngr_sent = at_end ? ngr : 0xFFFFFFFFu;
+    // these are used inside the loops below: keep them in registers instead of recomputing them from 64-bit values
+    uint32_t rel_end_r = rel_end, lim_r = lim, own_lo_r = own_lo, nl_lo_r = nl_lo, nl_hi_r = nl_hi, wr_end_r = wr_end, ngr_r = ngr;
+    asm volatile("" : "+r"(rel_end_r), "+r"(lim_r), "+r"(own_lo_r), "+r"(nl_lo_r), "+r"(nl_hi_r), "+r"(wr_end_r), "+r"(ngr_r), "+r"(ngr_sent));
+    const uint32_t sring = smem_u32(s) + (uint32_t)lane * 16u;           // this lane's 16 bytes of a cp.async
+    const uint8_t *glane = gsrc + lane * 16;
+
+    uint32_t cpos = 0, lh = 0, lt = 0, qh = 0, qn = 0;
+    uint32_t gi = 0, gw = 0;             // groups issued / groups that have arrived
     uint32_t over_eff = OVER;            // a line is looked at once this much text behind its start is classified (0 at the end)
-    uint32_t next_need = 0;              // the next stage can be issued once low has reached this
+    uint32_t next_need = 0;              // the next group can be issued once low has reached this
     Shp hp;                              // the shapes of the previous step (lane 31's is the next step's "previous")
     hp.w0 = hp.w1 = hp.w2 = hp.w3 = hp.P = hp.d = 0;
     uint32_t hp_start = 0;
@@ -346,40 +345,42 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     }
     __syncwarp();
 
-    // ---- bulk copies: as many stages as the ring has room for ----
+    // ---- text -> ring: cp.async (LDGSTS, 16 bytes per lane, L1 bypassed), one group per KiB, as many in flight as the ring has room for ----
     auto issue_allowed = [&]() {
-        // stage t overwrites what stage t - NST held; the last stage also needs room for the sentinel behind it
-        while (issued < nst) {
-            const uint32_t tt = issued + (issued == sent_stage ? 2u : 1u);
-            next_need = tt >= (uint32_t)NST ? (tt - NST) * STAGE : 0u;
-            if (low < next_need) return;
-            const uint32_t slot = issued % NST, off = issued * STAGE;
-            const uint32_t nb = rel_end - off < (uint32_t)STAGE ? rel_end - off : (uint32_t)STAGE;
-            const uint32_t mir = slot == 0 ? (nb < (uint32_t)MIRROR ? nb : (uint32_t)MIRROR) : 0u;
-            __syncwarp();
-            if (lane == 0) {
-                const uint32_t b = bar0 + 8u * slot;
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(nb + mir) : "memory");
-                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                                 smem_u32(s + slot * STAGE)),
-                             "l"(gsrc + off), "r"(nb), "r"(b)
-                             : "memory");
-                if (mir)
-                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                                     smem_u32(s + RING)),
-                                 "l"(gsrc + off), "r"(mir), "r"(b)
+        // group g overwrites what group g - NGR held
+        while (low >= next_need) {
+            const uint32_t goff = gi * GRP;
+            const uint32_t d0 = sring + (goff & (RING - 1));
+            const uint8_t *src = glane + goff;
+            const bool mirror = (goff & (RING - 1)) == 0u && lane < MIRROR / 16;     // the ring's first bytes once more behind its end
+            if (gi + 1u < ngr_r) {
+#pragma unroll
+                for (int j = 0; j < GRP / 512; j++)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 512u * j), "l"(src + 512 * j) : "memory");
+                if (mirror) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + (uint32_t)RING), "l"(src) : "memory");
+            } else {
+                // the chunk's last group: bytes beyond the text are not read (zero fill)
+                const uint32_t r0 = goff + (uint32_t)lane * 16u;
+#pragma unroll
+                for (int j = 0; j < GRP / 512; j++)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d0 + 512u * j), "l"(src + 512 * j),
+                                 "r"(r0 + 512u * j < rel_end_r ? 16u : 0u)
                                  : "memory");
+                if (mirror)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d0 + (uint32_t)RING), "l"(src), "r"(r0 < rel_end_r ? 16u : 0u) : "memory");
             }
-            issued++;
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            gi++;
+            // what group gi needs: the ring bytes of group gi - NGR free (one group more for the sentinel behind the last one)
+            const uint32_t tt = gi + (gi + 1u == ngr_sent ? 2u : 1u);
+            next_need = gi >= ngr_r ? 0xFFFFFFFFu : (tt >= (uint32_t)NGR ? (tt - NGR) * GRP : 0u);
         }
-        next_need = 0xFFFFFFFFu;
     };
-    auto wait_next = [&]() {                      // the next stage has been issued: wait for it (every lane observes the phase itself)
-        const uint32_t t = ready / STAGE;
-        const uint32_t b = bar0 + 8u * (t % NST), par = (t / NST) & 1u;
-        while (!mbar_try(b, par)) {}
-        if (t == sent_stage) {                    // sentinel: the data ends like a line ends
+    auto wait_for = [&](uint32_t g) {             // group g has been issued: wait for it (and so for all before it)
+        wait_groups(gi - (g + 1u));
+        __syncwarp();                             // every lane waited for its own copies
+        gw = g + 1u;
+        if (gw == ngr_sent) {                     // sentinel: the data ends like a line ends
 #pragma unroll
             for (int j = 0; j < 2; j++) {
                 uint32_t o = (dend_rel + (uint32_t)lane * 2u + j) & (RING - 1);
@@ -388,8 +389,6 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
             }
             __syncwarp();
         }
-        ready += STAGE;
-        cls_lim = ready >= rel_end ? rel_end + 1023u : ready;
     };
 
     // ---- phase 2: nb (<= 16) queued pairs, two lanes per pair ----
@@ -408,8 +407,8 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         if (act && P != 0u && st >= g_lo && st <= g_hi && n1 <= 12u && n2 <= 12u) {
             const unsigned long long g = (unsigned long long)st;      // offset from gsrc
             const uint32_t shn = (st & 3u) * 8u;
-            const uint32_t x0 = gword(gsrc, g), x1 = gword(gsrc, g + 4), x2 = gword(gsrc, g + 8), x3 = gword(gsrc, g + 12),
-                           x4 = gword(gsrc, g + 16);
+            const uint32_t *gp = gwords(gsrc, g);
+            const uint32_t x0 = __ldg(gp), x1 = __ldg(gp + 1), x2 = __ldg(gp + 2), x3 = __ldg(gp + 3), x4 = __ldg(gp + 4);
             const uint4 mk = LM[p1 > 16u ? 16u : p1];
             const uint32_t w0 = __funnelshift_r(x0, x1, shn) & mk.x, w1 = __funnelshift_r(x1, x2, shn) & mk.y;
             const uint32_t w2 = __funnelshift_r(x2, x3, shn) & mk.z, w3 = __funnelshift_r(x3, x4, shn) & mk.w;
@@ -455,11 +454,12 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
             const uint32_t nw = (act && !pslow) ? (rl + 3u) >> 2 : 0u;
             const uint32_t nwmax = __reduce_max_sync(0xffffffffu, nw);
             uint32_t diff = L.rlen ^ orl;
+            const uint32_t *rp = gwords(gsrc, r0);
+            const uint32_t rsh = ((uint32_t)r0 & 3u) * 8u;
             for (uint32_t j = 0; j < nwmax; j++) {
                 uint32_t w = 0;
                 if (j < nw) {
-                    const unsigned long long q = r0 + 4u * j;
-                    w = __funnelshift_r(gword(gsrc, q), gword(gsrc, q + 4), ((uint32_t)q & 3u) * 8u);
+                    w = __funnelshift_r(__ldg(rp + j), __ldg(rp + j + 1), rsh);
                     const uint32_t left = rl - 4u * j;
                     if (left < 4u) w &= (1u << (8u * left)) - 1u;
                 }
@@ -509,13 +509,12 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     };
 
     // ---- phase 1: nv (1..32) lines, entries lh .. lh + nv - 1 of the ring of line starts ----
-    auto step = [&](uint32_t nv, auto full_tag) {
-        constexpr bool FULL = decltype(full_tag)::value;
-        const bool actv = FULL || (uint32_t)lane < nv;
+    auto step = [&](uint32_t nv) {
+        const bool actv = (uint32_t)lane < nv;
         const uint32_t start = lines[(lh + (uint32_t)lane) & (LCAP - 1)];
         Shp h;
         h.w0 = h.w1 = h.w2 = h.w3 = h.P = h.d = 0;
-        if (actv) h = shape_of(s, spw, LM, start & (RING - 1), lim - start);
+        if (actv) h = shape_of(s, spw, LM, start & (RING - 1), lim_r - start);
         // the line before: lane - 1's, and for lane 0 lane 31's of the step before (one rotation does both)
         const bool l31 = lane == 31;
         const int src = (lane + 31) & 31;
@@ -524,7 +523,7 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         ph.w2 = __shfl_sync(0xffffffffu, l31 ? hp.w2 : h.w2, src); ph.w3 = __shfl_sync(0xffffffffu, l31 ? hp.w3 : h.w3, src);
         ph.P = __shfl_sync(0xffffffffu, l31 ? hp.P : h.P, src); ph.d = __shfl_sync(0xffffffffu, l31 ? hp.d : h.d, src);
         const uint32_t pstart = __shfl_sync(0xffffffffu, l31 ? hp_start : start, src);
-        const bool owned = actv && start > own_lo;
+        const bool owned = actv && start > own_lo_r;
         bool cand = owned;
         if (!have_prev && lane == 0) {
             // a stream's first line start is known to be one only behind a newline of the halo
@@ -546,7 +545,7 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         qn += __popc(cm);
         hp = h;
         hp_start = start;
-        if (!FULL && nv != 32u) {        // a short step (end of the chunk, or the ring was full): its last line goes to lane 31
+        if (nv != 32u) {               // a short step (end of the chunk, or the ring was full): its last line goes to lane 31
             const int last = (int)nv - 1;
             hp.w0 = __shfl_sync(0xffffffffu, h.w0, last); hp.w1 = __shfl_sync(0xffffffffu, h.w1, last);
             hp.w2 = __shfl_sync(0xffffffffu, h.w2, last); hp.w3 = __shfl_sync(0xffffffffu, h.w3, last);
@@ -555,43 +554,47 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         }
         low = __shfl_sync(0xffffffffu, hp_start, 31);
         have_prev = true;
-        lh += FULL ? 32u : nv;
+        lh += nv;
         __syncwarp();
     };
 
-    // ---- classify 1 KiB from cpos on: special bitmap + line starts ----
+    // ---- classify 2 KiB from cpos on (64 bytes per lane): special bitmap + line starts ----
     auto classify = [&]() {
-        const uint32_t c = cpos + 32u * (uint32_t)lane;
+        const uint32_t c = cpos + 64u * (uint32_t)lane;
         const uint32_t ro = c & (RING - 1);
-        const uint4 v0 = *reinterpret_cast<const uint4 *>(s + ro), v1 = *reinterpret_cast<const uint4 *>(s + ro + 16);
-        uint32_t m32 = nl16_of(v0) | (nl16_of(v1) << 16);
-        const uint32_t sp = sp16_of(v0) | (sp16_of(v1) << 16);
-        if (cpos >= nl_lo && cpos + 1024u <= nl_hi) {      // everywhere but in the stream's first and last iterations
-            spw[ro >> 5] = sp;
-            if (ro < (uint32_t)MIRROR) spw[(RING + ro) >> 5] = sp;
+        const uint4 *src = reinterpret_cast<const uint4 *>(s + ro);
+        const uint4 v0 = src[0], v1 = src[1], v2 = src[2], v3 = src[3];
+        uint32_t mlo = nl16_of(v0) | (nl16_of(v1) << 16), mhi = nl16_of(v2) | (nl16_of(v3) << 16);
+        const uint2 sp = make_uint2(sp16_of(v0) | (sp16_of(v1) << 16), sp16_of(v2) | (sp16_of(v3) << 16));
+        if (cpos >= nl_lo_r && cpos + (uint32_t)GRP <= nl_hi_r) {  // everywhere but in the chunk's first and last iterations
+            *reinterpret_cast<uint2 *>(spw + (ro >> 5)) = sp;
+            if (ro < (uint32_t)MIRROR) *reinterpret_cast<uint2 *>(spw + ((RING + ro) >> 5)) = sp;
         } else {
-            if (c < wr_end) {                              // beyond the stream the ring may hold older, live text
-                spw[ro >> 5] = sp;
-                if (ro < (uint32_t)MIRROR) spw[(RING + ro) >> 5] = sp;
+            if (c < wr_end_r) {                              // beyond the chunk the ring may hold older, live text
+                *reinterpret_cast<uint2 *>(spw + (ro >> 5)) = sp;
+                if (ro < (uint32_t)MIRROR) *reinterpret_cast<uint2 *>(spw + ((RING + ro) >> 5)) = sp;
             }
-            // newlines outside [nl_lo, nl_hi) open no line of this stream
-            int a = (int)nl_lo - (int)c, b = (long long)nl_hi - (long long)c > 32 ? 32 : (int)((long long)nl_hi - (long long)c);
-            a = a < 0 ? 0 : (a > 32 ? 32 : a);
-            b = b < 0 ? 0 : b;
-            const uint32_t lowb = b >= 32 ? 0xFFFFFFFFu : ((1u << b) - 1u), lowa = a >= 32 ? 0xFFFFFFFFu : ((1u << a) - 1u);
-            m32 &= b > a ? (lowb & ~lowa) : 0u;
+            // newlines outside [nl_lo, nl_hi) open no line of this chunk
+            const long long a = (long long)nl_lo_r - (long long)c, b = (long long)nl_hi_r - (long long)c;
+            const int a0 = a < 0 ? 0 : (a > 64 ? 64 : (int)a), b0 = b < 0 ? 0 : (b > 64 ? 64 : (int)b);
+            const unsigned long long lowb = b0 >= 64 ? ~0ull : ((1ull << b0) - 1ull), lowa = a0 >= 64 ? ~0ull : ((1ull << a0) - 1ull);
+            const unsigned long long keep = b0 > a0 ? (lowb & ~lowa) : 0ull;
+            mlo &= (uint32_t)keep;
+            mhi &= (uint32_t)(keep >> 32);
         }
-        const unsigned has = __ballot_sync(0xffffffffu, m32 != 0u);
-        const unsigned multi = __ballot_sync(0xffffffffu, (m32 & (m32 - 1u)) != 0u);
+        const unsigned hasl = __ballot_sync(0xffffffffu, mlo != 0u), hash = __ballot_sync(0xffffffffu, mhi != 0u);
+        const unsigned multi = __ballot_sync(0xffffffffu, ((mlo & (mlo - 1u)) | (mhi & (mhi - 1u))) != 0u);
         if (multi == 0u) {                         // at most one newline per 32 bytes: rank by ballot
-            if (m32) lines[(lt + __popc(has & ltmask)) & (LCAP - 1)] = c + __ffs(m32);
-            lt += __popc(has);
-            cpos += 1024u;
+            const uint32_t rl = lt + __popc(hasl & ltmask) + __popc(hash & ltmask);
+            if (mlo) lines[rl & (LCAP - 1)] = c + __ffs(mlo);
+            if (mhi) lines[(rl + (mlo ? 1u : 0u)) & (LCAP - 1)] = c + 32u + __ffs(mhi);
+            lt += __popc(hasl) + __popc(hash);
+            cpos += (uint32_t)GRP;
         } else {
             // general case: inclusive scan of the counts; only the lanes whose newlines all fit the ring of line
             // starts are consumed, the next iteration starts at the first lane that was not
             const uint32_t room = (uint32_t)LCAP - (lt - lh);
-            int cnt = __popc(m32), inc = cnt;
+            int cnt = __popc(mlo) + __popc(mhi), inc = cnt;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 int o = __shfl_up_sync(0xffffffffu, inc, d);
@@ -601,66 +604,62 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
             const int ncons = fit == 0xFFFFFFFFu ? 32 : __ffs(~fit) - 1;       // a prefix of the lanes (inc is monotone), >= 1
             uint32_t pos = lt + (uint32_t)(inc - cnt);
             if (lane < ncons) {
-                while (m32) {
-                    const int b = __ffs(m32);
-                    m32 &= m32 - 1u;
+                while (mlo) {
+                    const int b = __ffs(mlo);
+                    mlo &= mlo - 1u;
                     lines[pos & (LCAP - 1)] = c + (uint32_t)b;
+                    pos++;
+                }
+                while (mhi) {
+                    const int b = __ffs(mhi);
+                    mhi &= mhi - 1u;
+                    lines[pos & (LCAP - 1)] = c + 32u + (uint32_t)b;
                     pos++;
                 }
             }
             lt += (uint32_t)__shfl_sync(0xffffffffu, inc, ncons - 1);
-            cpos += 32u * (uint32_t)ncons;
+            cpos += 64u * (uint32_t)ncons;
         }
         __syncwarp();
     };
 
     // ---- the chunk ----
-    issue_allowed();
     for (;;) {
-        const uint32_t cnt = lt - lh;
-        if (cnt >= 32u && cpos - lines[(lh + 31u) & (LCAP - 1)] >= over_eff) {
-            step(32u, FullStep());
-            while (qn >= (uint32_t)QPAIRS) flush(QPAIRS);
-            if (low >= next_need) issue_allowed();
-            continue;
-        }
-        if (cpos + 1024u <= cls_lim && cnt <= (uint32_t)LCAP - 32u) {
+        // classify until 32 lines can be looked at, or until nothing more can be classified right now
+        uint32_t cnt;
+        bool canstep;
+        for (;;) {
+            cnt = lt - lh;
+            canstep = cnt >= 32u && cpos - lines[(lh + 31u) & (LCAP - 1)] >= over_eff;
+            if (canstep || cpos >= rel_end_r || cnt > (uint32_t)LCAP - 64u) break;
+            issue_allowed();                                  // usually one group: what the last iteration or step made room for
+            const uint32_t want = cpos + (uint32_t)GRP < rel_end_r ? cpos + (uint32_t)GRP : rel_end_r;
+            const uint32_t g = (want - 1u) / GRP;             // the group this iteration reads into
+            if (g >= gi) break;                               // the ring is full
+            if (g >= gw) wait_for(g);
             classify();
-            if (cpos >= rel_end) over_eff = 0u;
-            continue;
+            if (cpos >= rel_end_r) over_eff = 0u;
         }
-        // ---- the rare paths: waiting for text, the end of the chunk, a line longer than the ring ----
-        uint32_t nv = 0;
-        if (cpos < rel_end) {
-            if (cnt <= (uint32_t)LCAP - 32u) {
-                issue_allowed();
-                if (ready < issued * STAGE) { wait_next(); continue; }
-            }
-            // no room in the ring, because of one very long line: look at what can be looked at, then let go of the line before it
-            const uint32_t vi = lines[(lh + (uint32_t)lane) & (LCAP - 1)];
-            nv = __popc(__ballot_sync(0xffffffffu, (uint32_t)lane < cnt && cpos - vi >= (uint32_t)OVER));
-            if (!nv) {
-                const uint32_t st0 = cnt ? lines[lh & (LCAP - 1)] : cpos;      // nothing older than this is needed any more
-                if (low != st0 || hp.P) { hp.P = 0u; low = st0; continue; }
-                if (lane == 0) report(A.stats, file_base + cpos, SALSA_DATA_LINE_TOO_LONG);     // cannot happen: RING >> OVER + 2 * STAGE
-                break;
-            }
-        } else if (cnt) nv = cnt;              // < 32: the chunk's last lines
-        else break;
-        step(nv, PartStep());
+        uint32_t nv = 32u;
+        if (!canstep) {
+            // ---- the rare paths: the end of the chunk, a line longer than the ring ----
+            if (cpos < rel_end_r) {
+                // no room in the ring, because of one very long line: look at what can be looked at, then let go of the line before it
+                const uint32_t vi = lines[(lh + (uint32_t)lane) & (LCAP - 1)];
+                nv = __popc(__ballot_sync(0xffffffffu, (uint32_t)lane < cnt && cpos - vi >= (uint32_t)OVER));
+                if (!nv) {
+                    const uint32_t st0 = cnt ? lines[lh & (LCAP - 1)] : cpos;      // nothing older than this is needed any more
+                    if (low != st0 || hp.P) { hp.P = 0u; low = st0; continue; }
+                    if (lane == 0) report(A.stats, file_base + cpos, SALSA_DATA_LINE_TOO_LONG);     // cannot happen: RING >> OVER + 2 * GRP
+                    break;
+                }
+            } else if (cnt) nv = cnt < 32u ? cnt : 32u;     // the chunk's last lines
+            else break;
+        }
+        step(nv);
         while (qn >= (uint32_t)QPAIRS) flush(QPAIRS);
     }
     while (qn) flush(qn < (uint32_t)QPAIRS ? qn : (uint32_t)QPAIRS);
-    // every bulk copy of this chunk has arrived; the barriers start over with the next chunk
-    __syncwarp();
-    if (lane == 0) {
-#pragma unroll
-        for (int i = 0; i < NST; i++) {
-            asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar0 + 8u * i) : "memory");
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * i) : "memory");
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
     __syncwarp();
     }   // chunks
 
