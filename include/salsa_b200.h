@@ -66,6 +66,11 @@ int salsa_version(void);
 /* One context per (process, device).  Holds the device-side contig table. */
 int salsa_ctx_create(int device, salsa_ctx **out);
 void salsa_ctx_destroy(salsa_ctx *ctx);
+/* Tuning / test knob of the BED link scan (no counterpart in the reference; results never depend on it).  The scan
+ * marks "special" bytes either exactly (<= 0x20 or '/') or with a cheaper superset test (<= 0x2F); with the superset,
+ * lines whose first four fields hold one of the 14 characters 0x21..0x2E take the slow full parser.  mode 0 (default):
+ * a sample of the text decides per call; 1: always exact; 2: always the superset. */
+int salsa_ctx_scan_mode(salsa_ctx *ctx, int mode);
 
 /*
  * Contig table: replaces the three host dicts of make_links.py:37-48

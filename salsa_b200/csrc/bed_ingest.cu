@@ -120,7 +120,8 @@ static int scan_links(const LinkArgs &L, salsa_ctx *ctx, const void *d_bed, size
         return bedscan::launch_scan<LinkPolicy<SPARSE, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
     if (use_tile_scanner())
         return bedscan::launch_scan<LinkPolicy<SPARSE, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
-    return bedstream::launch_stream<LinkEmit<SPARSE>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
+    return bedstream::launch_stream<LinkEmit<SPARSE>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, ctx->scan_mode, ctx->names_punct,
+                                                      ctx->d_mode, st);
 }
 
 __global__ void stats_reset_kernel(uint64_t *s)

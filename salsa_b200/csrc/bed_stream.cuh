@@ -161,15 +161,16 @@ __device__ __forceinline__ Shp shape_of(const uint8_t *s, const uint32_t *spw, c
     Shp h;
     const uint32_t i = p >> 5, sh = p & 31u;
     const uint32_t a0 = spw[i], a1 = spw[i + 1], a2 = spw[i + 2];
-    uint32_t m0 = __funnelshift_r(a0, a1, sh), m1 = __funnelshift_r(a1, a2, sh);
-    // every step: distance to the next special byte, then shift it out (a distance of 32 = none in reach)
-    const uint32_t d1 = __clz(__brev(m0));
-    m0 = __funnelshift_rc(m0, m1, d1 + 1u); m1 = __funnelshift_rc(m1, 0u, d1 + 1u);
-    const uint32_t d2 = __clz(__brev(m0));
-    m0 = __funnelshift_rc(m0, m1, d2 + 1u); m1 = __funnelshift_rc(m1, 0u, d2 + 1u);
-    const uint32_t d3 = __clz(__brev(m0));
-    m0 = __funnelshift_rc(m0, m1, d3 + 1u); m1 = __funnelshift_rc(m1, 0u, d3 + 1u);
-    const uint32_t d4 = m0 ? __clz(__brev(m0)) : 32u + __clz(__brev(m1));
+    // the 64 bits from the line's start on, bit-reversed: the next special byte is then the leading one (one FLO), and
+    // shifting left drops it.  A distance of 32 = none in reach.
+    uint32_t rh = __brev(__funnelshift_r(a0, a1, sh)), rl = __brev(__funnelshift_r(a1, a2, sh));
+    const uint32_t d1 = __clz(rh);
+    rh = __funnelshift_lc(rl, rh, d1 + 1u); rl = __funnelshift_lc(0u, rl, d1 + 1u);
+    const uint32_t d2 = __clz(rh);
+    rh = __funnelshift_lc(rl, rh, d2 + 1u); rl = __funnelshift_lc(0u, rl, d2 + 1u);
+    const uint32_t d3 = __clz(rh);
+    rh = __funnelshift_lc(rl, rh, d3 + 1u); rl = __funnelshift_lc(0u, rl, d3 + 1u);
+    const uint32_t d4 = rh ? __clz(rh) : 32u + __clz(rl);
     const uint32_t p1 = d1, p2 = p1 + 1u + d2, p3 = p2 + 1u + d3, p4 = p3 + 1u + d4;
     const uint32_t c1 = s[p + p1], c2 = s[p + p2], c3 = s[p + p3], c4 = s[p + p4];
     // no short-circuit: every lane runs the same few instructions
@@ -210,6 +211,48 @@ __device__ __forceinline__ bool ring_digits12(const uint8_t *s, const uint4 *LM,
     const uint32_t v2 = __dp4a(u2, 0x0000010Au, 0u) * 100u + __dp4a(u2, 0x010A0000u, 0u);
     val = (long long)((unsigned long long)(v0 * 10000u + v1) * 10000ull + v2);
     return bad == 0u;
+}
+
+// ---- which "special byte" test the classification runs ----
+// Exact: byte <= 0x20 or byte == '/' (7 instructions per 4-byte word).  Cheap: byte <= 0x2F (3 per word) -- a superset:
+// a line whose first four fields hold one of the 14 characters 0x21..0x2E ('.', '-', '#', ...) then merely fails the
+// separator checks of phase 1 and goes through the full parser, so results are identical either way and only speed is
+// at stake.  The sample kernel looks at three windows of the text and picks the cheap test when such characters are no
+// more frequent than a strand column would make them (one per line).
+__device__ __forceinline__ uint32_t le_bytes_0x2f(uint32_t w)
+{
+    uint32_t t = (w & 0x7F7F7F7Fu) + 0x50505050u;     // bit 7 set iff (b & 0x7f) > 0x2f
+    return ~(t | w) & 0x80808080u;
+}
+__device__ __forceinline__ uint32_t cheap16_of(const uint4 &v)
+{
+    return pack16(le_bytes_0x2f(v.x), le_bytes_0x2f(v.y), le_bytes_0x2f(v.z), le_bytes_0x2f(v.w));
+}
+
+struct CheapTest { static constexpr bool value = true; };
+struct ExactTest { static constexpr bool value = false; };
+
+constexpr int SAMPLE_WIN = 65536;
+__global__ void __launch_bounds__(256) bed_sample_kernel(ScanArgs A, int names_punct, int *d_mode)
+{
+    __shared__ unsigned int cnt[2];            // newlines, bytes in 0x21..0x2E
+    if (threadIdx.x < 2) cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned long long n = A.dend - A.mis;
+    unsigned int nl = 0, pu = 0;
+    for (int w = 0; w < 3; w++) {
+        unsigned long long b = w == 0 ? 0ull : (w == 1 ? n / 2 : (n > (unsigned long long)SAMPLE_WIN ? n - SAMPLE_WIN : 0ull));
+        if (w > 0 && n <= (unsigned long long)SAMPLE_WIN) break;
+        for (unsigned long long i = b + threadIdx.x; i < b + SAMPLE_WIN && i < n; i += 256) {
+            const uint32_t c = A.abase[A.mis + i];
+            nl += c == 10u;
+            pu += (c - 0x21u) <= 0x0Du;
+        }
+    }
+    atomicAdd(&cnt[0], nl);
+    atomicAdd(&cnt[1], pu);
+    __syncthreads();
+    if (threadIdx.x == 0) *d_mode = (!names_punct && cnt[1] <= cnt[0] + cnt[0] / 16u + 2u) ? 1 : 0;
 }
 
 // cp.async.wait_group takes an immediate: wait until at most `ahead` of this thread's groups are still in flight
@@ -269,10 +312,12 @@ __device__ __forceinline__ int lookup_global(const DevTable &t, const uint8_t *g
 }
 
 template <class Emit>
-__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t chunk_bytes, uint32_t nchunks)
+__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t chunk_bytes, uint32_t nchunks, const int *d_mode)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // ptxas would rather re-read %tid and redo the address arithmetic inside the loops than keep these in registers
+    asm volatile("" : "+r"(lane), "+r"(warp));
     uint4 *LM = reinterpret_cast<uint4 *>(smem);          // LM[e]: the low e bytes of a 16-byte window
     if (threadIdx.x < 17) {
         uint32_t m[4];
@@ -284,6 +329,8 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         LM[threadIdx.x] = make_uint4(m[0], m[1], m[2], m[3]);
     }
     uint8_t *base = smem + 17 * 16 + (size_t)warp * WARP_SMEM;
+    asm volatile("" : "+l"(base));
+    __builtin_assume(__isShared(base));
     uint8_t *s = base + FRONT;                                                  // the ring
     uint32_t *spw = reinterpret_cast<uint32_t *>(s + RING + MIRROR);            // special bitmap, bit per ring byte
     uint32_t *lines = spw + SPW;                                                // ring of line starts (stream offsets)
@@ -293,6 +340,7 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
 
     uint32_t nlines = 0, npairs = 0;
     const unsigned ltmask = (1u << lane) - 1u;
+    const bool cheap = *d_mode != 0;             // which special-byte test (same for the whole launch)
     const unsigned long long dend = A.dend, dend16 = (dend + 15ull) & ~15ull;
     // Chunks are dealt round robin: at any time the warps of the whole GPU work side by side in one window of the text
     // (a few hundred MB), which keeps the TLB and the DRAM pages they touch few.
@@ -301,11 +349,13 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     const unsigned long long S0 = (unsigned long long)ck * chunk_bytes;
     unsigned long long S1 = S0 + chunk_bytes;
     if (S1 > dend || ck + 1 == nchunks) S1 = dend;
-    const unsigned long long lo = S0 >= (unsigned long long)HALO ? S0 - HALO : 0ull;      // first byte loaded
+    unsigned long long lo = S0 >= (unsigned long long)HALO ? S0 - HALO : 0ull;            // first byte loaded
+    asm volatile("" : "+l"(lo));             // (kept in registers: see lane / warp above)
     unsigned long long hi = S1 + HALO;                                                    // one past the last byte classified
     const bool at_end = hi >= dend16;
     if (at_end) hi = dend16;
     const uint8_t *gsrc = A.abase + lo;
+    asm volatile("" : "+l"(gsrc));
     // ---- the same, relative to lo (32 bit) ----
     const uint32_t rel_end = (uint32_t)(hi - lo);
     const uint32_t dend_rel = at_end ? (uint32_t)(dend - lo) : 0xFFFFFF00u;
@@ -316,7 +366,8 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     const uint32_t nl_hi = (uint32_t)(nlh - lo);
     const uint32_t ngr = (rel_end + GRP - 1) / GRP;                     // cp.async groups of this chunk
     const uint32_t wr_end = at_end ? rel_end + 64u : rel_end;          // bitmap words are written up to here (sentinel included)
-    const uint64_t file_base = A.base_offset - (uint64_t)A.mis + lo;    // file offset of chunk offset 0
+    uint64_t file_base = A.base_offset - (uint64_t)A.mis + lo;          // file offset of chunk offset 0
+    asm volatile("" : "+l"(file_base));
     // phase 2 reads a plain line's words from global memory: keep clear of both ends of the buffer
     const uint32_t g_lo = lo >= 16ull ? 0u : 16u - (uint32_t)lo;
     const uint32_t g_hi = !at_end ? 0xFFFFFF00u : (dend_rel >= 192u ? dend_rel - 192u : 0u);
@@ -328,6 +379,7 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     asm volatile("" : "+r"(rel_end_r), "+r"(lim_r), "+r"(own_lo_r), "+r"(nl_lo_r), "+r"(nl_hi_r), "+r"(wr_end_r), "+r"(ngr_r), "+r"(ngr_sent));
     const uint32_t sring = smem_u32(s) + (uint32_t)lane * 16u;           // this lane's 16 bytes of a cp.async
     const uint8_t *glane = gsrc + lane * 16;
+    asm volatile("" : "+l"(glane));
 
     uint32_t cpos = 0, lh = 0, lt = 0, qh = 0, qn = 0;
     uint32_t gi = 0, gw = 0;             // groups issued / groups that have arrived
@@ -559,13 +611,15 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     };
 
     // ---- classify 2 KiB from cpos on (64 bytes per lane): special bitmap + line starts ----
-    auto classify = [&]() {
+    auto classify = [&](auto cheap_tag) {
+        constexpr bool CHEAP = decltype(cheap_tag)::value;
         const uint32_t c = cpos + 64u * (uint32_t)lane;
         const uint32_t ro = c & (RING - 1);
         const uint4 *src = reinterpret_cast<const uint4 *>(s + ro);
         const uint4 v0 = src[0], v1 = src[1], v2 = src[2], v3 = src[3];
         uint32_t mlo = nl16_of(v0) | (nl16_of(v1) << 16), mhi = nl16_of(v2) | (nl16_of(v3) << 16);
-        const uint2 sp = make_uint2(sp16_of(v0) | (sp16_of(v1) << 16), sp16_of(v2) | (sp16_of(v3) << 16));
+        const uint2 sp = CHEAP ? make_uint2(cheap16_of(v0) | (cheap16_of(v1) << 16), cheap16_of(v2) | (cheap16_of(v3) << 16))
+                               : make_uint2(sp16_of(v0) | (sp16_of(v1) << 16), sp16_of(v2) | (sp16_of(v3) << 16));
         if (cpos >= nl_lo_r && cpos + (uint32_t)GRP <= nl_hi_r) {  // everywhere but in the chunk's first and last iterations
             *reinterpret_cast<uint2 *>(spw + (ro >> 5)) = sp;
             if (ro < (uint32_t)MIRROR) *reinterpret_cast<uint2 *>(spw + ((RING + ro) >> 5)) = sp;
@@ -637,7 +691,8 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
             const uint32_t g = (want - 1u) / GRP;             // the group this iteration reads into
             if (g >= gi) break;                               // the ring is full
             if (g >= gw) wait_for(g);
-            classify();
+            if (cheap) classify(CheapTest());
+            else classify(ExactTest());
             if (cpos >= rel_end_r) over_eff = 0u;
         }
         uint32_t nv = 32u;
@@ -674,7 +729,7 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
 
 template <class Emit>
 int launch_stream(const typename Emit::Args &EA, const DevTable &t, const void *d_bed, size_t nbytes, uint64_t base_offset,
-                  uint64_t *stats, cudaStream_t st)
+                  uint64_t *stats, int scan_mode, int names_punct, int *d_mode, cudaStream_t st)
 {
     if (nbytes == 0) return SALSA_OK;
     ScanArgs A;
@@ -707,7 +762,10 @@ int launch_stream(const typename Emit::Args &EA, const DevTable &t, const void *
     if (nchunks > 0x7fffffffull) SALSA_FAIL(SALSA_ERR_ARG, "BED chunk too large (%zu bytes)", nbytes);
     uint64_t ctas = (nchunks + WARPS - 1) / WARPS;
     if (ctas > (uint64_t)ctas_per_dev[dev]) ctas = (uint64_t)ctas_per_dev[dev];
-    bed_stream_kernel<Emit><<<(unsigned)ctas, WARPS * 32, CTA_SMEM, st>>>(EA, A, (uint32_t)cb, (uint32_t)nchunks);
+    // scan_mode: 0 = the sample kernel decides, 1 = exact special-byte test, 2 = cheap one
+    if (scan_mode == 0) bed_sample_kernel<<<1, 256, 0, st>>>(A, names_punct, d_mode);
+    else CUDA_TRY(cudaMemsetAsync(d_mode, scan_mode == 2 ? 1 : 0, 1, st));
+    bed_stream_kernel<Emit><<<(unsigned)ctas, WARPS * 32, CTA_SMEM, st>>>(EA, A, (uint32_t)cb, (uint32_t)nchunks, d_mode);
     CUDA_TRY(cudaGetLastError());
     return SALSA_OK;
 }

@@ -64,6 +64,9 @@ struct salsa_ctx {
     cudaStream_t s_copy, s_comp;
     cudaEvent_t ev_copy[2], ev_comp[2];
     bool streams_ready;
+    // streaming scanner: special-byte test (0 auto, 1 exact, 2 cheap), contig names with a byte in 0x21..0x2E, device flag
+    int scan_mode, names_punct;
+    int *d_mode;
 };
 int salsa_ctx_streams(salsa_ctx *c);
 

@@ -38,6 +38,10 @@ extern "C" int salsa_ctx_create(int device, salsa_ctx **out)
     salsa_ctx *c = (salsa_ctx *)calloc(1, sizeof(salsa_ctx));
     if (!c) SALSA_FAIL(SALSA_ERR_NOMEM, "out of host memory");
     c->device = device;
+    if (cudaMalloc(&c->d_mode, 16) != cudaSuccess || cudaMemset(c->d_mode, 0, 16) != cudaSuccess) {
+        free(c);
+        SALSA_FAIL(SALSA_ERR_CUDA, "salsa_ctx_create: cudaMalloc failed");
+    }
     *out = c;
     return SALSA_OK;
 }
@@ -58,6 +62,7 @@ extern "C" void salsa_ctx_destroy(salsa_ctx *c)
     cudaSetDevice(c->device);
     free_table(c);
     cudaFree(c->d_avoid);
+    cudaFree(c->d_mode);
     if (c->streams_ready) {
         cudaStreamDestroy(c->s_copy);
         cudaStreamDestroy(c->s_comp);
@@ -80,6 +85,13 @@ int salsa_ctx_streams(salsa_ctx *c)
 }
 
 extern "C" int32_t salsa_names_count(const salsa_ctx *c) { return c ? c->n : 0; }
+
+extern "C" int salsa_ctx_scan_mode(salsa_ctx *c, int mode)
+{
+    if (!c || mode < 0 || mode > 2) SALSA_FAIL(SALSA_ERR_ARG, "salsa_ctx_scan_mode: mode must be 0 (auto), 1 (exact) or 2 (cheap)");
+    c->scan_mode = mode;
+    return SALSA_OK;
+}
 
 extern "C" int salsa_names_build(salsa_ctx *c, const char *blob, const int64_t *off, int32_t n, const int64_t *len_floor,
                                  const uint32_t *flags)
@@ -131,6 +143,9 @@ extern "C" int salsa_names_build(salsa_ctx *c, const char *blob, const int64_t *
     CUDA_TRY(cudaMemcpy(c->d_meta, c->h_meta, ((size_t)n + 1) * sizeof(ContigMeta), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(c->d_blob, blob, (size_t)off[n], cudaMemcpyHostToDevice));
     c->n = n;
+    c->names_punct = 0;
+    for (int64_t i = 0; i < off[n]; i++)
+        if ((unsigned char)blob[i] - 0x21u <= 0x0Du) { c->names_punct = 1; break; }
     c->t.slots = (const NameSlot *)c->d_slots;
     c->t.mask = nslots - 1;
     c->t.meta = (const ContigMeta *)c->d_meta;

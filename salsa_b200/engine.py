@@ -53,6 +53,11 @@ class Engine:
         self.sparse = None
         self.stats = torch.zeros(4, dtype=torch.int64, device=self.device)
 
+    def scan_mode(self, mode):
+        """Special-byte test of the link scan: 0 = a sample of the text decides (default), 1 = exact, 2 = cheap
+        superset.  Results never depend on it (include/salsa_b200.h: salsa_ctx_scan_mode)."""
+        check(self.L.salsa_ctx_scan_mode(self.ctx, int(mode)))
+
     def close(self):
         if self.ctx:
             self.L.salsa_ctx_destroy(self.ctx)

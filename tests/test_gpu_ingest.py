@@ -11,10 +11,13 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
 
 
-@pytest.fixture(scope='module')
-def eng():
+@pytest.fixture(scope='module', params=['auto', 'exact', 'cheap'])
+def eng(request):
+    """One engine per special-byte test of the link scan (picked by a sample of the text / forced exact / forced to
+    the cheap superset test): every case below must give the same result in all three."""
     from salsa_b200.engine import Engine
     e = Engine(0)
+    e.scan_mode({'auto': 0, 'exact': 1, 'cheap': 2}[request.param])
     yield e
     e.close()
 
