@@ -46,7 +46,7 @@ constexpr int WARPS = SALSA_STREAM_WARPS;   // warps per CTA (they share nothing
 constexpr int SPW = (RING + MIRROR) / 32 + 4;
 constexpr uint32_t CHUNK_MIN = 16384;       // shortest chunk worth a warp
 #ifndef SALSA_STREAM_CHUNK
-#define SALSA_STREAM_CHUNK 131072
+#define SALSA_STREAM_CHUNK 262144
 #endif
 constexpr uint32_t CHUNK_MAX = SALSA_STREAM_CHUNK;   // bytes of text a warp walks through before it takes the next chunk
 static_assert(RING % GRP == 0 && NGR >= 4 && NGR <= 8 && (RING & (RING - 1)) == 0, "ring geometry");
