@@ -9,7 +9,8 @@ The reference has no tests of its own and its scripts are Python-2 only; parity 
 fast_scaled_scores / RE_sites is PINNED by tests/golden/links_ref.json, which the reference's own
 scripts produced under tests/golden/ref_py2emu.py (the twin and the C oracle both reproduce it), and
 update_bed's BED pass by tests/golden/pipeline_ref/ (a stage-by-stage run of the reference's programs);
-correct_links remains unpinned (the reference needs boost::graph, absent here).  Deviations from a
+correct_links by tests/golden/correct_links_ref.json (the unmodified correct_links.cpp built against the
+boost stand-in of oracle/_shim).  Deviations from a
 literal transliteration are exactly the Python-2 semantics that Python 3
 changed, each emulated explicitly:
   * ``str(float)``  -> ``py2_str`` ('%.12g' + '.0'),  evidence
@@ -240,8 +241,8 @@ def re_sites(assembly, enzyme):
 
 
 def correct_links(gfa, hic_links):
-    """correct_links.cpp:70-354 as a second, independent restatement (the reference needs
-    boost::graph and cannot be compiled here: PARITY UNPINNED).  Dijkstra on unit weights is a
+    """correct_links.cpp:70-354 as a second, independent restatement (pinned by
+    tests/golden/correct_links_ref.json, the compiled reference's stdout).  Dijkstra on unit weights is a
     breadth-first search.  Emulated C++ behaviours: unordered_map::operator[] inserting id 0 for
     unknown names, the vecS graph growing to the largest edge endpoint, (long)FLT_MAX failing the
     INT_MIN/INT_MAX test, ostream's '%g' formatting of doubles, the inconsistent `added` keys.

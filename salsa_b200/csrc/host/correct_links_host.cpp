@@ -4,10 +4,11 @@
 //
 // Host program, no GPU work: the reference re-orients Hi-C links with the help of the assembly
 // graph -- a direct GFA edge between the two contig ends wins, otherwise the orientation with
-// the shortest graph path.  The reference needs boost::graph (not vendored, absent here, so it
-// cannot be compiled: parity is pinned only by oracle/py_twin.correct_links).  All GFA edges
-// have weight 1.0, so Dijkstra distances are breadth-first hop counts; they are computed once
-// per source vertex and cached instead of twice per link.
+// the shortest graph path.  The reference runs boost Dijkstra twice per link; all GFA edges
+// have weight 1.0, so the distances are breadth-first hop counts, computed here once per source
+// vertex and cached.  Parity: tests/golden/correct_links_ref.json is the stdout of the unmodified
+// reference source (built against a test-only stand-in for its four boost::graph calls,
+// oracle/_shim); tests/test_correct_links.py holds this program to it.
 //
 // Behaviours kept on purpose (they shape the output):
 //   * unordered_map::operator[] on unknown names yields vertex id 0 AND inserts the name

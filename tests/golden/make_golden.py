@@ -6,6 +6,10 @@ been compiled by oracle/Makefile):   python tests/golden/make_golden.py
 coverage_ref.json : stdout of the UNMODIFIED reference programs
                     (oracle/_ref/break_contigs_start, break_contigs) on the
                     deterministic cases in tests/cases.py.
+correct_links_ref.json : stdout of the UNMODIFIED reference correct_links.cpp,
+                    compiled against the test-only boost stand-in
+                    oracle/_shim (boost itself is not in the image), on
+                    cases.CORRECT_LINKS_CASES.
 links_twin.json   : vectors from the line-by-line py3 twin (oracle/py_twin.py),
                     a second, independent restatement.
 links_ref.json    : the same vectors plus a messy-text case, produced by the
@@ -53,6 +57,16 @@ def main():
                             '-i', '2', '-s', '100'], capture_output=True, check=True)
         cov['joins'][nm] = sorted(r.stdout.decode().splitlines())
     json.dump(cov, open(os.path.join(HERE, 'coverage_ref.json'), 'w'), indent=1, sort_keys=True)
+
+    # correct_links: stdout of the UNMODIFIED reference source compiled against the boost stand-in of oracle/_shim
+    cl = {}
+    for nm, mk in cases.CORRECT_LINKS_CASES.items():
+        gfa, links = mk()
+        open(d + '/g.gfa', 'w').write(gfa)
+        open(d + '/hl.txt', 'w').write(links)
+        r = subprocess.run([oracle.REF_DIR + '/correct_links', '-g', d + '/g.gfa', '-l', d + '/hl.txt'], capture_output=True, check=True)
+        cl[nm] = r.stdout.decode().split('\n')[:-1]
+    json.dump(cl, open(os.path.join(HERE, 'correct_links_ref.json'), 'w'), indent=1, sort_keys=True)
 
     # links / RE / scaled vectors from the py3 twin on a small synthetic case
     asm, rec, bed = synth.small_case(ncontig=12, genome=200000, npairs=3000, seed=1)
