@@ -202,6 +202,21 @@ int salsa_links_partition(const uint64_t *d_keys, const uint64_t *d_counts, size
                           uint64_t *h_part_counts, void *stream);
 int salsa_sparse_add(const uint64_t *d_in_keys, const uint64_t *d_in_counts, size_t n, uint64_t *d_keys,
                      uint64_t *d_counts, size_t capacity, uint32_t *d_full_flag, void *stream);
+/*
+ * The same merge without compaction, sort or host round trip (the link key space of make_links.py:140-144; integer
+ * sums, any shard order).  salsa_sparse_partition walks the sender's hash table ONCE and appends every link to the
+ * segment of its owner = mix64(key) % nparts.  A segment is [u64 count][u64 pad][u64 keys[slot_cap]]
+ * [u32 counts[slot_cap]] -- 12 bytes per link and salsa_sparse_segment_bytes(slot_cap) bytes in all; d_segments holds
+ * nparts of them back to back, so the exchange is ONE all-to-all with equal splits.  slot_cap (a multiple of 4) bounds
+ * the links per owner: *d_overflow (caller-zeroed) becomes 1 when a segment was too small or a count did not fit 32
+ * bits -- retry with a larger slot_cap.  salsa_sparse_add_segments adds the nparts segments a rank received into its
+ * table (*d_full_flag as in salsa_sparse_add).  Both are asynchronous on `stream`.
+ */
+size_t salsa_sparse_segment_bytes(size_t slot_cap);
+int salsa_sparse_partition(const uint64_t *d_keys, const uint64_t *d_counts, size_t capacity, int32_t nparts,
+                           size_t slot_cap, void *d_segments, uint32_t *d_overflow, void *stream);
+int salsa_sparse_add_segments(const void *d_segments, int32_t nparts, size_t slot_cap, uint64_t *d_keys,
+                              uint64_t *d_counts, size_t capacity, uint32_t *d_full_flag, void *stream);
 
 /*
  * Python-2 str(float) on the device.  The reference passes scores between

@@ -57,6 +57,9 @@ SIGNATURES = {
     'salsa_sort_pairs_u64': (C.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_size_t), c_void_p]),
     'salsa_links_partition': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     'salsa_sparse_add': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p]),
+    'salsa_sparse_segment_bytes': (c_size_t, [c_size_t]),
+    'salsa_sparse_partition': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_size_t, c_void_p, c_void_p, c_void_p]),
+    'salsa_sparse_add_segments': (C.c_int, [c_void_p, c_i32, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p]),
     'salsa_g12': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_void_p]),
     'salsa_links_score': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 10),
     'salsa_scaled_scratch_bytes': (c_size_t, [c_i32]),

@@ -255,6 +255,134 @@ extern "C" int salsa_sparse_add(const uint64_t *d_in_keys, const uint64_t *d_in_
     return SALSA_OK;
 }
 
+// ---- sparse merge, fused: hash table -> per-owner segments in ONE pass, no sort, no host round trip ----
+// A segment is what one peer receives: [u64 count][u64 pad][u64 keys[slot_cap]][u32 counts[slot_cap]] -- 12 bytes per
+// link, every segment the same size, so the exchange is ONE all-to-all with equal splits whose sizes the host knows
+// without asking the device.  The receiver reads `count` from each segment it got.
+namespace {
+
+constexpr int PT = 256;          // threads per block
+constexpr int PER = 8;           // table slots per thread and batch
+
+__host__ __device__ inline size_t seg_bytes(size_t slot_cap) { return 16 + slot_cap * 12; }     // slot_cap % 4 == 0
+
+__global__ void seg_init_kernel(uint8_t *seg, int nparts, size_t segb)
+{
+    if (threadIdx.x < nparts) {
+        uint64_t *h = reinterpret_cast<uint64_t *>(seg + (size_t)threadIdx.x * segb);
+        h[0] = 0;
+        h[1] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(PT) seg_partition_kernel(const uint64_t *keys, const uint64_t *counts, size_t cap, int nparts,
+                                                           size_t slot_cap, uint8_t *seg, size_t segb, unsigned int *overflow)
+{
+    __shared__ unsigned int h[MAXPARTS];
+    __shared__ unsigned long long base[MAXPARTS];
+    const size_t nbatch = (cap + (size_t)PT * PER - 1) / ((size_t)PT * PER);
+    for (size_t b = blockIdx.x; b < nbatch; b += gridDim.x) {
+        if (threadIdx.x < MAXPARTS) h[threadIdx.x] = 0;
+        __syncthreads();
+        uint64_t k[PER], c[PER];
+        int part[PER];
+        unsigned int rank[PER];
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            const size_t i = (b * PER + j) * PT + threadIdx.x;          // coalesced: consecutive threads, consecutive slots
+            k[j] = i < cap ? keys[i] : ~0ull;
+            c[j] = (k[j] != ~0ull) ? counts[i] : 0;
+            part[j] = -1;
+            if (c[j]) {
+                part[j] = (int)(salsa_mix64(k[j]) % (uint64_t)nparts);
+                rank[j] = atomicAdd(&h[part[j]], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < nparts)
+            base[threadIdx.x] = h[threadIdx.x]
+                                    ? atomicAdd(reinterpret_cast<unsigned long long *>(seg + (size_t)threadIdx.x * segb),
+                                                (unsigned long long)h[threadIdx.x])
+                                    : 0ull;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            if (part[j] < 0) continue;
+            const unsigned long long o = base[part[j]] + rank[j];
+            if (o >= slot_cap || c[j] > 0xFFFFFFFFull) { atomicExch(overflow, 1u); continue; }
+            uint8_t *sp = seg + (size_t)part[j] * segb + 16;
+            reinterpret_cast<uint64_t *>(sp)[o] = k[j];
+            reinterpret_cast<uint32_t *>(sp + slot_cap * 8)[o] = (uint32_t)c[j];
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) seg_add_kernel(const uint8_t *seg, int nparts, size_t slot_cap, size_t segb, uint64_t *keys,
+                                                      uint64_t *counts, uint64_t cap_mask, unsigned int *full)
+{
+    const int p = blockIdx.y;
+    const uint8_t *sp = seg + (size_t)p * segb;
+    uint64_t n = *reinterpret_cast<const uint64_t *>(sp);
+    if (n > slot_cap) n = slot_cap;                 // the sender flagged the overflow
+    const uint64_t *ik = reinterpret_cast<const uint64_t *>(sp + 16);
+    const uint32_t *ic = reinterpret_cast<const uint32_t *>(sp + 16 + slot_cap * 8);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint64_t key = ik[i];
+        uint64_t slot = salsa_mix64(key) & cap_mask;
+        bool done = false;
+        for (uint64_t probe = 0; probe <= cap_mask; probe++) {
+            unsigned long long k = ((volatile unsigned long long *)keys)[slot];
+            if (k == ~0ull) {
+                unsigned long long old = atomicCAS((unsigned long long *)&keys[slot], ~0ull, (unsigned long long)key);
+                k = (old == ~0ull || old == key) ? key : old;
+            }
+            if (k == key) {
+                atomicAdd((unsigned long long *)&counts[slot], (unsigned long long)ic[i]);
+                done = true;
+                break;
+            }
+            slot = (slot + 1) & cap_mask;
+        }
+        if (!done) atomicExch(full, 1u);
+    }
+}
+
+}   // namespace
+
+extern "C" size_t salsa_sparse_segment_bytes(size_t slot_cap) { return seg_bytes((slot_cap + 3) & ~(size_t)3); }
+
+extern "C" int salsa_sparse_partition(const uint64_t *d_keys, const uint64_t *d_counts, size_t capacity, int32_t nparts,
+                                      size_t slot_cap, void *d_segments, uint32_t *d_overflow, void *stream)
+{
+    if (nparts < 1 || nparts > MAXPARTS) SALSA_FAIL(SALSA_ERR_ARG, "salsa_sparse_partition: 1..%d parts", MAXPARTS);
+    if (!d_keys || !d_counts || !d_segments || !d_overflow || capacity == 0 || slot_cap == 0 || (slot_cap & 3))
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_sparse_partition: bad argument (slot_cap must be a multiple of 4)");
+    cudaStream_t st = as_stream(stream);
+    const size_t segb = seg_bytes(slot_cap);
+    seg_init_kernel<<<1, MAXPARTS, 0, st>>>((uint8_t *)d_segments, nparts, segb);
+    size_t nbatch = (capacity + (size_t)PT * PER - 1) / ((size_t)PT * PER);
+    unsigned grid = (unsigned)(nbatch < 148 * 8 ? nbatch : 148 * 8);
+    seg_partition_kernel<<<grid, PT, 0, st>>>(d_keys, d_counts, capacity, nparts, slot_cap, (uint8_t *)d_segments, segb, d_overflow);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
+extern "C" int salsa_sparse_add_segments(const void *d_segments, int32_t nparts, size_t slot_cap, uint64_t *d_keys, uint64_t *d_counts,
+                                         size_t capacity, uint32_t *d_full_flag, void *stream)
+{
+    if (nparts < 1 || nparts > MAXPARTS) SALSA_FAIL(SALSA_ERR_ARG, "salsa_sparse_add_segments: 1..%d parts", MAXPARTS);
+    if (!d_segments || !d_keys || !d_counts || !d_full_flag || capacity == 0 || (capacity & (capacity - 1)) || slot_cap == 0 ||
+        (slot_cap & 3))
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_sparse_add_segments: bad argument");
+    size_t per = (slot_cap + 255) / 256;
+    dim3 grid((unsigned)(per < 148 * 4 ? per : 148 * 4), (unsigned)nparts);
+    seg_add_kernel<<<grid, 256, 0, as_stream(stream)>>>((const uint8_t *)d_segments, nparts, slot_cap, seg_bytes(slot_cap), d_keys,
+                                                        d_counts, capacity - 1, d_full_flag);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}
+
 // key-sorts (key, count) pairs; used after compacting a sparse table.  The
 // radix sort is CUB's (library code: this step is off the hot path).
 extern "C" int salsa_sort_pairs_u64(uint64_t *d_keys_in, uint64_t *d_vals_in, uint64_t *d_keys_out, uint64_t *d_vals_out,

@@ -4,8 +4,11 @@
 The data path shards naturally -- read pairs are independent -- so the only
 exchange step is the merge of the per-GPU tables:
   dense  : all-reduce(sum) of the uint64 table (288 MB for 3,000 contigs);
-  sparse : hash-partition the compacted (key, count) pairs on the key, one
-           all-to-all, then add into the owner's table.
+  sparse : every link of a rank's hash table goes into the segment of its owner
+           = mix64(key) % world (one pass over the table, no compaction, no sort),
+           ONE all-to-all with equal splits moves the segments, and the receiver
+           adds them into its table (exchange_segments; the older compact ->
+           partition -> three all-to-alls route is exchange_sparse).
 Integer sums: results do not depend on the number of shards.
 """
 import numpy as np
@@ -154,3 +157,102 @@ class EngineOps:
         check(L.salsa_links_compact(tk.data_ptr(), tc.data_ptr(), cap, ok.data_ptr(), oc.data_ptr(), m.value, scratch.data_ptr(),
                                     C.byref(m), st))
         return ok[:m.value], oc[:m.value]
+
+
+# ---------------------------------------------------------------- segments: one pass, one all-to-all
+def segment_bytes(slot_cap):
+    """[u64 count][u64 pad][u64 keys[slot_cap]][u32 counts[slot_cap]]  (include/salsa_b200.h: salsa_sparse_partition)"""
+    assert slot_cap % 4 == 0
+    return 16 + 12 * slot_cap
+
+
+class TorchSegmentOps:
+    """numpy restatement of salsa_sparse_partition / salsa_sparse_add_segments for the CPU (gloo) tests of the
+    exchange plumbing; the GPU path uses EngineSegmentOps."""
+
+    def partition(self, tkeys, tcounts, nparts, slot_cap):
+        k, c = tkeys.numpy(), tcounts.numpy()
+        livek, livec = k[(k != -1) & (c != 0)], c[(k != -1) & (c != 0)]
+        owner = (TorchOps.mix64(torch.from_numpy(livek)).numpy().view(np.uint64) % np.uint64(nparts)).astype(np.int64)
+        segb = segment_bytes(slot_cap)
+        buf = np.zeros(nparts * segb, np.uint8)
+        overflow = False
+        for p in range(nparts):
+            kk, cc = livek[owner == p], livec[owner == p]
+            if len(kk) > slot_cap or (len(cc) and cc.max() > 0xFFFFFFFF):
+                overflow = True
+                kk, cc = kk[:slot_cap], np.minimum(cc[:slot_cap], 0xFFFFFFFF)
+            seg = buf[p * segb:(p + 1) * segb]
+            seg[:8].view(np.uint64)[0] = len(kk)
+            seg[16:16 + 8 * len(kk)].view(np.int64)[:] = kk
+            seg[16 + 8 * slot_cap:16 + 8 * slot_cap + 4 * len(cc)].view(np.uint32)[:] = cc.astype(np.uint32)
+        return torch.from_numpy(buf), overflow
+
+    def add(self, recv, nparts, slot_cap):
+        buf, segb = recv.numpy(), segment_bytes(slot_cap)
+        acc = {}
+        for p in range(nparts):
+            seg = buf[p * segb:(p + 1) * segb]
+            n = int(seg[:8].view(np.uint64)[0])
+            kk = seg[16:16 + 8 * n].view(np.int64)
+            cc = seg[16 + 8 * slot_cap:16 + 8 * slot_cap + 4 * n].view(np.uint32)
+            for a, b in zip(kk.tolist(), cc.tolist()):
+                acc[a] = acc.get(a, 0) + b
+        ks = sorted(acc)
+        return torch.tensor(ks, dtype=torch.int64), torch.tensor([acc[a] for a in ks], dtype=torch.int64)
+
+
+class EngineSegmentOps:
+    """salsa_sparse_partition / salsa_sparse_add_segments through the C ABI.  Buffers are kept between calls (a step of
+    the merge allocates nothing after the first one); nothing here synchronises: overflow / table-full flags are device
+    words that the caller reads when it wants to (flags())."""
+
+    def __init__(self, eng, out_capacity):
+        self.eng, self.outcap = eng, out_capacity
+        dev = eng.device
+        self.tk = torch.empty(out_capacity, dtype=torch.int64, device=dev)
+        self.tc = torch.empty(out_capacity, dtype=torch.int64, device=dev)
+        self.flag = torch.zeros(2, dtype=torch.int32, device=dev)        # [0] a segment overflowed, [1] owner's table full
+        self.send = self.recv = None
+
+    def _bufs(self, nbytes):
+        if self.send is None or self.send.numel() != nbytes:
+            self.send = torch.empty(nbytes, dtype=torch.uint8, device=self.eng.device)
+            self.recv = torch.empty(nbytes, dtype=torch.uint8, device=self.eng.device)
+        return self.send, self.recv
+
+    def partition(self, tkeys, tcounts, nparts, slot_cap):
+        from ._lib import check
+        L = self.eng.L
+        send, _ = self._bufs(nparts * L.salsa_sparse_segment_bytes(slot_cap))
+        check(L.salsa_sparse_partition(tkeys.data_ptr(), tcounts.data_ptr(), tkeys.numel(), nparts, slot_cap, send.data_ptr(),
+                                       self.flag[0:1].data_ptr(), torch.cuda.current_stream().cuda_stream))
+        return send, None
+
+    def add(self, recv, nparts, slot_cap):
+        from ._lib import check
+        L, st = self.eng.L, torch.cuda.current_stream().cuda_stream
+        check(L.salsa_sparse_reset(self.tk.data_ptr(), self.tc.data_ptr(), self.outcap, st))
+        check(L.salsa_sparse_add_segments(recv.data_ptr(), nparts, slot_cap, self.tk.data_ptr(), self.tc.data_ptr(), self.outcap,
+                                          self.flag[1:2].data_ptr(), st))
+        return self.tk, self.tc
+
+    def flags(self):
+        """(segment overflow, owner table full) -- synchronises."""
+        f = self.flag.cpu().tolist()
+        return bool(f[0]), bool(f[1])
+
+
+def exchange_segments(tkeys, tcounts, ops, slot_cap, group=None):
+    """The sparse merge in one pass and one collective: `tkeys`/`tcounts` are a rank's whole open-addressing table
+    (empty slots: key -1); every live link is appended to the segment of owner = mix64(key) % world, the segments are
+    exchanged by ONE all-to-all with equal splits (no sizes to agree on, so no host round trip), and the receiver adds
+    what it got into its table.  Returns what ops.add returns: the links this rank owns."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    send, _ = ops.partition(tkeys, tcounts, world, slot_cap)
+    if world > 1:
+        recv = ops.recv if getattr(ops, 'recv', None) is not None else torch.empty_like(send)
+        dist.all_to_all_single(recv, send, group=group)
+    else:
+        recv = send
+    return ops.add(recv, world, slot_cap)

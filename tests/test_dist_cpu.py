@@ -82,6 +82,23 @@ for ks, cs in zip(gk, gc):
         assert k not in got          # owned by exactly one rank
         got[k] = c
 assert got == want
+# the one-pass route: whole hash tables in, one equal-split all-to-all of segments, owners add
+from salsa_b200.dist import TorchSegmentOps, exchange_segments
+cap = 8192
+tk = np.full(cap, -1, np.int64); tc = np.zeros(cap, np.int64)
+slots = rng.choice(cap, len(keys), replace=False)          # any placement: the walk does not depend on the hash
+tk[slots] = keys; tc[slots] = counts
+sk, sc = exchange_segments(torch.from_numpy(tk), torch.from_numpy(tc), TorchSegmentOps(), slot_cap=4096)
+h = TorchOps.mix64(sk).numpy().view(np.uint64) %% np.uint64(w)
+assert (h == r).all()
+g2k = [None] * w; g2c = [None] * w
+dist.all_gather_object(g2k, sk.tolist()); dist.all_gather_object(g2c, sc.tolist())
+got2 = {}
+for ks, cs in zip(g2k, g2c):
+    for k, c in zip(ks, cs):
+        assert k not in got2
+        got2[k] = c
+assert got2 == want
 # dense merge: all-reduce(sum)
 t = torch.full((64,), r + 1, dtype=torch.int64)
 merge_dense(t)

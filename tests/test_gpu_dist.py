@@ -40,13 +40,76 @@ def test_partition_and_sparse_add_kernels():
     eng.close()
 
 
+def test_segment_partition_and_add_kernels():
+    """salsa_sparse_partition / salsa_sparse_add_segments against their numpy statement (dist.TorchSegmentOps), with
+    every "rank" emulated on one GPU: the segments of nparts senders are re-assembled by owner and added."""
+    from salsa_b200._lib import check
+    from salsa_b200.dist import EngineSegmentOps, TorchSegmentOps, segment_bytes
+    from salsa_b200.engine import Engine
+    eng = Engine(0)
+    L, dev = eng.L, eng.device
+    st = torch.cuda.current_stream().cuda_stream
+    rng = np.random.default_rng(5)
+    cap = 1 << 18
+    for nparts in (1, 2, 3, 8):
+        tables, want = [], {}
+        for r in range(nparts):                       # one hash table per emulated sender, overlapping key sets
+            keys = np.unique(rng.integers(0, 2 ** 40, 60000)).astype(np.int64)
+            counts = rng.integers(1, 1000, len(keys)).astype(np.int64)
+            tk = torch.empty(cap, dtype=torch.int64, device=dev)
+            tc = torch.empty(cap, dtype=torch.int64, device=dev)
+            check(L.salsa_sparse_reset(tk.data_ptr(), tc.data_ptr(), cap, st))
+            full = torch.zeros(1, dtype=torch.int32, device=dev)
+            dk, dc = torch.from_numpy(keys).to(dev), torch.from_numpy(counts).to(dev)
+            check(L.salsa_sparse_add(dk.data_ptr(), dc.data_ptr(), len(keys), tk.data_ptr(), tc.data_ptr(), cap, full.data_ptr(), st))
+            assert int(full.item()) == 0
+            tables.append((tk, tc))
+            for k, c in zip(keys.tolist(), counts.tolist()):
+                want[k] = want.get(k, 0) + c
+        slot_cap = 65536
+        segb = segment_bytes(slot_cap)
+        assert L.salsa_sparse_segment_bytes(slot_cap) == segb
+        sends = []
+        for tk, tc in tables:
+            ops = EngineSegmentOps(eng, 1 << 19)
+            send, _ = ops.partition(tk, tc, nparts, slot_cap)
+            assert ops.flags() == (False, False)
+            ref, ovf = TorchSegmentOps().partition(tk.cpu(), tc.cpu(), nparts, slot_cap)
+            assert not ovf
+            for p in range(nparts):                   # same multiset per segment (order inside a segment is free)
+                a = send[p * segb:(p + 1) * segb].cpu().numpy()
+                b = ref[p * segb:(p + 1) * segb].numpy()
+                na, nb = int(a[:8].view(np.uint64)[0]), int(b[:8].view(np.uint64)[0])
+                assert na == nb
+                ka, kb = a[16:16 + 8 * na].view(np.int64), b[16:16 + 8 * nb].view(np.int64)
+                ca, cb = a[16 + 8 * slot_cap:][:4 * na].view(np.uint32), b[16 + 8 * slot_cap:][:4 * nb].view(np.uint32)
+                assert sorted(zip(ka.tolist(), ca.tolist())) == sorted(zip(kb.tolist(), cb.tolist()))
+            sends.append(send.clone())
+        got = {}
+        for owner in range(nparts):                   # what the all-to-all would deliver to `owner`
+            recv = torch.cat([s_[owner * segb:(owner + 1) * segb] for s_ in sends])
+            ops = EngineSegmentOps(eng, 1 << 19)
+            ok, oc = ops.add(recv, nparts, slot_cap)
+            assert ops.flags() == (False, False)
+            live = (ok != -1) & (oc != 0)
+            for k, c in zip(ok[live].cpu().tolist(), oc[live].cpu().tolist()):
+                assert k not in got
+                got[k] = c
+        assert got == want
+    # a segment that is too small is reported, never silently short
+    ops = EngineSegmentOps(eng, 1 << 19)
+    ops.partition(tables[0][0], tables[0][1], 2, 1000)
+    assert ops.flags()[0] is True
+    eng.close()
+
+
 WORKER = r'''
 import os, sys
 sys.path.insert(0, %r)
 import numpy as np, torch, torch.distributed as dist
 import oracle
 from salsa_b200 import synth
-from salsa_b200.dist import shard_ranges, merge_dense, exchange_sparse, EngineOps
+from salsa_b200.dist import shard_ranges, merge_dense, exchange_sparse, EngineOps, EngineSegmentOps, exchange_segments
 from salsa_b200.engine import Engine
 rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
 torch.cuda.set_device(local)
@@ -74,6 +137,21 @@ eng.stats_read()
 k, c, m = eng._compact()
 ok, oc = exchange_sparse(k[:m], c[:m], EngineOps(eng))
 mine = dict(zip(ok.cpu().tolist(), oc.cpu().tolist()))
+parts = [None] * world
+dist.all_gather_object(parts, mine)
+merged = {}
+for p in parts:
+    for kk, vv in p.items():
+        assert kk not in merged
+        merged[kk] = vv
+assert merged == want
+# sparse, one pass and one all-to-all: whole hash tables in, segments exchanged, owners add
+keys, cnts, cap = eng.sparse
+sops = EngineSegmentOps(eng, 1 << 18)
+ok, oc = exchange_segments(keys, cnts, sops, slot_cap=1 << 16)
+assert sops.flags() == (False, False)
+live = (ok != -1) & (oc != 0)
+mine = dict(zip(ok[live].cpu().tolist(), oc[live].cpu().tolist()))
 parts = [None] * world
 dist.all_gather_object(parts, mine)
 merged = {}
