@@ -179,7 +179,10 @@ def sparse_leg(args, eng, dev, rank, world):
     eng.ingest_device(bed)
     eng.stats_read()
     keys, cnts, cap = eng.sparse
-    live = int(((keys != -1) & (cnts != 0)).sum().item())
+    live_t = ((keys != -1) & (cnts != 0)).sum()
+    if world > 1:
+        dist.all_reduce(live_t, op=dist.ReduceOp.MAX)       # every rank must use the same segment size
+    live = int(live_t.item())
     slot_cap = (int(live / world * 1.15) + 4096) // 4 * 4
     cap = outcap = 1 << 20
     while cap < 2 * live:                 # tables at load <= 0.5: this rank's, and its share of the merged one
