@@ -53,8 +53,7 @@ extern "C" {
                                       that precedes a tile boundary, exceed
                                       SALSA_MAX_LINE bytes (library limit)       */
 
-#define SALSA_DATA_AVOID_CHAIN 9   /* avoid mode: more than 64 consecutive lines on avoid-listed
-                                      contigs directly before a tile boundary (library limit)     */
+#define SALSA_DATA_AVOID_CHAIN 9   /* no longer produced: the avoid-mode walk-back has no limit any more */
 
 #define SALSA_MAX_LINE 1024        /* bytes; see SALSA_DATA_LINE_TOO_LONG */
 

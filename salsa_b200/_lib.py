@@ -24,6 +24,7 @@ class SalsaError(RuntimeError):
         self.code = code
 
 
+DATA_TABLE_FULL = 6
 DATA_ERRORS = {1: 'IndexError', 2: 'ValueError', 3: 'KeyError', 4: 'ZeroDivisionError', 5: 'LineTooLong', 6: 'TableFull'}
 
 

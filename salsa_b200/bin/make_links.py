@@ -65,7 +65,6 @@ def main(argv=None):
     nm, lens, rl, rr, has_re, avoid = load_tables(args.directory, iteration)
     eng = engine()
     eng.set_contigs(nm, lens, rl, rr, has_re, avoid)
-    eng.begin_links('auto')
     print('bedfile started', file=sys.stderr)
     from salsa_b200.reproject import resident_bed
     try:
@@ -73,11 +72,12 @@ def main(argv=None):
         bed = resident_bed(args.mapping, eng.device, load=_common.KEEP_RESIDENT)
     except MemoryError:
         bed = None
+    # dense table, or (fragmented assemblies) a sparse one that grows like the reference's dict; stats_read inside
+    # raises DataError where the reference would raise
     if bed is not None:
-        eng.ingest_device(bed)
+        eng.ingest_links(lambda: eng.ingest_device(bed))
     else:
-        eng.ingest_file(args.mapping)      # streamed through a staging buffer; nothing stays on the device
-    eng.stats_read()                      # raises DataError where the reference would raise
+        eng.ingest_links(lambda: eng.ingest_file(args.mapping))   # streamed through a staging buffer; nothing stays on the device
     print('bedfile loaded', file=sys.stderr)
     sc = eng.score_links()
     print(sc['n'])

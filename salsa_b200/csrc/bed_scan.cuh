@@ -508,7 +508,7 @@ __device__ __forceinline__ Shape line_shape(const Smem &S, int p, int sent)
 // pair is formed with is the last NON-SKIPPED line.  A line whose contig is in no
 // avoid pair can never be skipped: chains of dependent decisions only run through
 // consecutive "involved" lines and are resolved by walking back to the nearest
-// line that is certainly kept and replaying forward.
+// line that is certainly kept and replaying forward (no limit on the length of the walk).
 __device__ __forceinline__ bool avoid_has(const DevTable &t, int a, int b)
 {
     if (a < 0 || b < 0 || a == b) return false;
@@ -531,7 +531,10 @@ __device__ Rec parse_global_line(const ScanArgs &A, const Smem &S, long long st,
 }
 
 // Thread 0: was entry 0 (the line before the first owned line) skipped, and if so which
-// earlier line is the effective "previous" of the first owned line?
+// earlier line is the effective "previous" of the first owned line?  Walks back through global
+// memory to the nearest line that is certainly kept (its contig is in no avoid pair, or it is the
+// buffer's first line) -- however far that is -- and replays the reference's loop forward from there
+// (make_links.py:72-74: a skipped line does not become prev_line).
 template <class Policy>
 __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
 {
@@ -541,13 +544,9 @@ __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
     const long long g0 = sb + (long long)S.lines[0];
     const long long mis = (long long)A.mis;
     if (!idv_inv(v0) || g0 <= mis) return;            // certainly kept (or the buffer's first line: always "previous")
-    constexpr int MAXC = 64;
-    long long cst[MAXC];
-    int clen[MAXC], cid[MAXC];
-    int nc = 0;
-    long long cur = g0;
-    bool anchored = false;
-    while (nc < MAXC) {
+    long long cur = g0, prev_st = 0;
+    int prev_len = 0, prev_id = -1;
+    for (;;) {                                        // back to the anchor
         long long e = cur - 1;                        // the '\n' that ends the previous line
         long long st = e;
         while (st > mis && A.abase[st - 1] != '\n' && e - st <= SALSA_MAX_LINE) st--;
@@ -556,23 +555,22 @@ __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
             return;
         }
         Rec r = parse_global_line<Policy>(A, S, st, (int)(e - st));
-        cst[nc] = st; clen[nc] = (int)(e - st); cid[nc] = r.id;
-        nc++;
         bool inv = r.id >= 0 && (A.t.meta[r.id].flags & CTG_INVOLVED);
-        if (!inv || st <= mis) { anchored = true; break; }
+        if (!inv || st <= mis) { prev_st = st; prev_len = (int)(e - st); prev_id = r.id; break; }
         cur = st;
     }
-    if (!anchored) {                                  // library limit: > 64 consecutive lines on avoid-listed contigs before a tile
-        report(A.stats, A.base_offset + (uint64_t)(g0 - mis), SALSA_DATA_AVOID_CHAIN);
-        return;
+    long long pos = prev_st + prev_len + 1;           // forward again: every line between the anchor and entry 0
+    while (pos < g0) {
+        long long en = pos;
+        while (en < g0 - 1 && A.abase[en] != '\n') en++;
+        Rec r = parse_global_line<Policy>(A, S, pos, (int)(en - pos));     // (its length was checked on the way back)
+        if (!avoid_has(A.t, prev_id, r.id)) { prev_st = pos; prev_len = (int)(en - pos); prev_id = r.id; }
+        pos = en + 1;
     }
-    int prev = nc - 1;                                // the anchor; cst[0] is the line right before entry 0
-    for (int k = nc - 2; k >= 0; k--)
-        if (!avoid_has(A.t, cid[prev], cid[k])) prev = k;
-    if (avoid_has(A.t, cid[prev], idv_id(v0))) {
-        *S.ext = parse_global_line<Policy>(A, S, cst[prev], clen[prev]);   // stays in the spare buffer for byte compares
+    if (avoid_has(A.t, prev_id, idv_id(v0))) {
+        *S.ext = parse_global_line<Policy>(A, S, prev_st, prev_len);       // stays in the spare buffer for byte compares
         S.extinfo[0] = 1;
-        S.extinfo[1] = cid[prev];
+        S.extinfo[1] = prev_id;
     }
 }
 

@@ -123,7 +123,7 @@ class Engine:
             self.table = torch.zeros(ncell, dtype=torch.int64, device=self.device)
             self.sparse = None
         else:
-            cap = 1 << 20
+            cap = 1 << 10
             while cap < (sparse_capacity or (1 << 24)):
                 cap <<= 1
             keys = torch.empty(cap, dtype=torch.int64, device=self.device)
@@ -131,6 +131,26 @@ class Engine:
             check(self.L.salsa_sparse_reset(keys.data_ptr(), cnts.data_ptr(), cap, st))
             self.sparse = (keys, cnts, cap)
             self.table = None
+
+    def ingest_links(self, ingest, mode='auto', sparse_capacity=None):
+        """begin_links(mode) + ingest() + stats_read().  A sparse table that turns out too small is not an error of
+        the input -- the reference's dict simply grows (make_links.py:140-144) -- so on SALSA_DATA_TABLE_FULL the table
+        is made four times larger and the BED is ingested again, until it fits or the GPU has no room for the table.
+        `ingest` is a callable that feeds the whole BED (ingest_device / ingest_file calls)."""
+        cap = sparse_capacity
+        while True:
+            self.begin_links(mode, sparse_capacity=cap)
+            ingest()
+            try:
+                return self.stats_read()
+            except DataError as e:
+                if e.code != _lib.DATA_TABLE_FULL or self.mode != 'sparse':
+                    raise
+                cap = self.sparse[2] * 4
+                free, _ = torch.cuda.mem_get_info(self.device)
+                if cap * 16 > free + self.sparse[2] * 16:
+                    raise MemoryError('sparse link table of %d slots does not fit the GPU' % cap)
+                self.sparse = None
 
     def ingest_device(self, bed, base_offset=0):
         """bed: uint8 CUDA tensor whose first byte starts a line.  Asynchronous."""

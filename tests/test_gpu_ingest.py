@@ -153,6 +153,29 @@ def test_host_streaming(eng, oracle_lib, chunk):
     assert got == want
 
 
+def test_sparse_table_grows_like_the_reference_dict(eng, oracle_lib):
+    """A sparse table that is too small is not the input's fault: ingest_links re-ingests with a larger one
+    (make_links.py:140-144: the dict just grows) and the result equals the oracle's."""
+    from salsa_b200 import synth
+    from salsa_b200.engine import DataError
+    asm, rec, bed = synth.small_case(ncontig=120, genome=3_000_000, npairs=60000, seed=21, noise=0.5)
+    want, _ = oracle_dict(oracle_lib, bed, asm.names, asm.lengths)
+    assert len(want) > 3000
+    n = asm.ncontig
+    eng.set_contigs(asm.names, np.asarray(asm.lengths, np.int64), np.ones(n, np.int64), np.ones(n, np.int64))
+    dev_bed = torch.frombuffer(bytearray(bed), dtype=torch.uint8).to(eng.device)
+    eng.begin_links('sparse', sparse_capacity=1024)          # far too small: the kernel reports it ...
+    eng.ingest_device(dev_bed)
+    with pytest.raises(DataError) as ge:
+        eng.stats_read()
+    assert ge.value.code == 6
+    st = eng.ingest_links(lambda: eng.ingest_device(dev_bed), mode='sparse', sparse_capacity=1024)     # ... and this path recovers
+    assert eng.sparse[2] >= 4096
+    f, s, e, c = eng.links()
+    got = {(eng.names[a], eng.names[b], int(x)): int(y) for a, b, x, y in zip(f, s, e, c)}
+    assert got == want and sum(got.values()) == st.pairs
+
+
 def test_empty_and_tiny(eng, oracle_lib):
     names, L = [b'A', b'B'], [1000, 2000]
     for bed in (b'', b'\n', b'A 1 2 r/1', b'A 1 2 r/1\n', b'A 100 200 r1/1\nB 1900 1990 r1/2\n', b'A 100 200 r1/1\nB 1900 1990 r1/2'):
