@@ -156,11 +156,13 @@ int salsa_bed_ingest_sparse(salsa_ctx *ctx, const void *d_bed, size_t nbytes, ui
  * Convenience for host-resident BEDs (what make_links.py does with a file):
  * streams h_bed through two device staging buffers of `chunk_bytes` each
  * (caller-owned, d_stage[2*chunk_bytes]) with copies overlapped with the
- * kernel, splitting at line starts.  h_bed should be pinned for full PCIe
- * speed.  Synchronises before returning.
+ * kernel, splitting at line starts (with an avoid set: at lines whose contig is
+ * in no avoid pair).  h_bed should be pinned for full PCIe speed.  The work is
+ * ordered after what the caller enqueued on `stream` (zeroing the table) and
+ * `stream` waits for it; the call returns when h_bed has been consumed.
  */
 int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, size_t nbytes, void *d_stage,
-                                size_t chunk_bytes, uint64_t *d_table, uint64_t *d_stats);
+                                size_t chunk_bytes, uint64_t *d_table, uint64_t *d_stats, void *stream);
 
 /*
  * Table -> ordered edge list (replaces the dict walk of make_links.py:161-169;

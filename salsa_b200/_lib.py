@@ -52,7 +52,7 @@ SIGNATURES = {
     'salsa_bed_ingest_dense': (C.c_int, [c_void_p, c_void_p, c_size_t, c_u64, c_void_p, c_void_p, c_void_p]),
     'salsa_sparse_reset': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     'salsa_bed_ingest_sparse': (C.c_int, [c_void_p, c_void_p, c_size_t, c_u64, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p]),
-    'salsa_bed_ingest_dense_host': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),
+    'salsa_bed_ingest_dense_host': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     'salsa_links_compact_scratch_bytes': (c_size_t, [c_size_t]),
     'salsa_links_compact': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_u64), c_void_p]),
     'salsa_sort_pairs_u64': (C.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_size_t), c_void_p]),

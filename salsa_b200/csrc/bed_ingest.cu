@@ -8,6 +8,10 @@
 // HBM traffic = the BED bytes once; everything else lives in smem / L2.
 #include <stdlib.h>
 
+#include <algorithm>
+#include <string>
+#include <vector>
+
 #include "bed_scan.cuh"
 #include "bed_stream.cuh"
 
@@ -198,36 +202,54 @@ extern "C" int salsa_bed_ingest_sparse(salsa_ctx *ctx, const void *d_bed, size_t
     return scan_links<true>(L, ctx, d_bed, nbytes, base_offset, d_stats, as_stream(stream));
 }
 
+// Is the line that starts at p (and ends before lim) on a contig that occurs in some avoid pair?  (str.split()'s first token)
+static bool line_involved(const salsa_ctx *ctx, const char *p, const char *lim)
+{
+    const std::vector<std::string> *inv = (const std::vector<std::string> *)ctx->h_involved;
+    if (!inv || inv->empty()) return false;
+    auto ws = [](char c) { return c == ' ' || (c >= 9 && c <= 13); };
+    while (p < lim && *p != '\n' && ws(*p)) p++;
+    const char *e = p;
+    while (e < lim && !ws(*e)) e++;
+    return std::binary_search(inv->begin(), inv->end(), std::string(p, (size_t)(e - p)));
+}
+
 // Host-resident BED: chunked H2D copies overlapped with the kernel.  Chunks
-// start on line starts and overlap by exactly one line (see salsa_b200.h).
+// start on line starts and overlap by exactly one line (see salsa_b200.h); with
+// an avoid set, on a line whose contig is in no avoid pair (it can never be skipped).
 extern "C" int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, size_t nbytes, void *d_stage,
-                                           size_t chunk_bytes, uint64_t *d_table, uint64_t *d_stats)
+                                           size_t chunk_bytes, uint64_t *d_table, uint64_t *d_stats, void *stream)
 {
     int rc = check_ingest_args(ctx, d_stage, nbytes, d_table, d_stats);
     if (rc) return rc;
     if (!h_bed && nbytes) SALSA_FAIL(SALSA_ERR_ARG, "h_bed is NULL");
     if (chunk_bytes < 4 * (size_t)SALSA_MAX_LINE || (chunk_bytes & 15))
         SALSA_FAIL(SALSA_ERR_ARG, "chunk_bytes must be a multiple of 16 and >= %d", 4 * SALSA_MAX_LINE);
-    if (ctx->t.navoid > 0)
-        SALSA_FAIL(SALSA_ERR_UNSUPPORTED, "salsa_bed_ingest_dense_host: with an avoid set, chunk on the host at lines whose "
-                                          "contig is in no avoid pair and call salsa_bed_ingest_dense per chunk");
     rc = salsa_ctx_streams(ctx);
     if (rc) return rc;
     const char *h = (const char *)h_bed;
     size_t pos = 0;
     int k = 0;
     LinkArgs L{d_table, NULL, 0};
-    // the caller's earlier work on d_table / d_stats (zeroing) must be complete
-    CUDA_TRY(cudaDeviceSynchronize());
+    // the caller's earlier work on d_table / d_stats (zeroing) was enqueued on `stream`: both internal streams follow it
+    CUDA_TRY(cudaEventRecord(ctx->ev_user, as_stream(stream)));
+    CUDA_TRY(cudaStreamWaitEvent(ctx->s_copy, ctx->ev_user, 0));
+    CUDA_TRY(cudaStreamWaitEvent(ctx->s_comp, ctx->ev_user, 0));
     while (pos < nbytes) {
         size_t end = pos + chunk_bytes < nbytes ? pos + chunk_bytes : nbytes;
         size_t next = nbytes;
         if (end < nbytes) {
-            // last complete line inside [pos, end)
+            // the last complete line inside [pos, end) is shared: it ends this chunk and starts the next one
             const char *nl = (const char *)memrchr(h + pos, '\n', end - pos);
-            if (!nl || nl == h + pos) SALSA_FAIL(SALSA_ERR_ARG, "BED line longer than the staging chunk near byte %zu", pos);
-            const char *pl = (const char *)memrchr(h + pos, '\n', (size_t)(nl - (h + pos)));
-            if (!pl) SALSA_FAIL(SALSA_ERR_ARG, "BED line longer than the staging chunk near byte %zu", pos);
+            const char *pl = nl && nl > h + pos ? (const char *)memrchr(h + pos, '\n', (size_t)(nl - (h + pos))) : NULL;
+            while (pl && ctx->t.navoid > 0 && line_involved(ctx, pl + 1, nl)) {
+                // the shared line could be skipped by the avoid rule: move the cut back to a line that cannot
+                nl = pl;
+                pl = nl > h + pos ? (const char *)memrchr(h + pos, '\n', (size_t)(nl - (h + pos))) : NULL;
+            }
+            if (!nl || !pl)
+                SALSA_FAIL(SALSA_ERR_ARG, ctx->t.navoid > 0 ? "no line outside the avoid list to split the BED at near byte %zu (or a line longer than the staging chunk)"
+                                                             : "BED line longer than the staging chunk near byte %zu", pos);
             end = (size_t)(nl - h) + 1;
             next = (size_t)(pl - h) + 1;      // the last line is the next chunk's "previous"
         }
@@ -242,6 +264,9 @@ extern "C" int salsa_bed_ingest_dense_host(salsa_ctx *ctx, const void *h_bed, si
         pos = next;
         k++;
     }
+    // what the caller enqueues on `stream` next sees the finished table; the host buffer is free when this returns
+    CUDA_TRY(cudaEventRecord(ctx->ev_user, ctx->s_comp));
+    CUDA_TRY(cudaStreamWaitEvent(as_stream(stream), ctx->ev_user, 0));
     CUDA_TRY(cudaStreamSynchronize(ctx->s_comp));
     return SALSA_OK;
 }

@@ -67,6 +67,12 @@ struct salsa_ctx {
     // streaming scanner: special-byte test (0 auto, 1 exact, 2 cheap), contig names with a byte in 0x21..0x2E, device flag
     int scan_mode, names_punct;
     int *d_mode;
+    // host copy of the names of contigs that occur in an avoid pair, sorted (salsa_bed_ingest_dense_host cuts its
+    // chunks at lines that can never be skipped); '\0'-separated blob + offsets
+    char *h_blob;
+    int64_t *h_off;
+    void *h_involved;          // std::vector<std::string> *
+    cudaEvent_t ev_user;       // orders the internal streams after the caller's stream
 };
 int salsa_ctx_streams(salsa_ctx *c);
 

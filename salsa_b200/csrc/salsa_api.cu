@@ -3,6 +3,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <string>
 #include <vector>
 
 #include "common.cuh"
@@ -48,6 +49,10 @@ extern "C" int salsa_ctx_create(int device, salsa_ctx **out)
 
 static void free_table(salsa_ctx *c)
 {
+    free(c->h_blob);
+    free(c->h_off);
+    c->h_blob = NULL;
+    c->h_off = NULL;
     cudaFree(c->d_slots);
     cudaFree(c->d_meta);
     cudaFree(c->d_blob);
@@ -63,7 +68,9 @@ extern "C" void salsa_ctx_destroy(salsa_ctx *c)
     free_table(c);
     cudaFree(c->d_avoid);
     cudaFree(c->d_mode);
+    delete (std::vector<std::string> *)c->h_involved;
     if (c->streams_ready) {
+        cudaEventDestroy(c->ev_user);
         cudaStreamDestroy(c->s_copy);
         cudaStreamDestroy(c->s_comp);
         for (int i = 0; i < 2; i++) { cudaEventDestroy(c->ev_copy[i]); cudaEventDestroy(c->ev_comp[i]); }
@@ -80,6 +87,7 @@ int salsa_ctx_streams(salsa_ctx *c)
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&c->ev_comp[i], cudaEventDisableTiming));
     }
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming));
     c->streams_ready = true;
     return SALSA_OK;
 }
@@ -142,6 +150,13 @@ extern "C" int salsa_names_build(salsa_ctx *c, const char *blob, const int64_t *
     CUDA_TRY(cudaMemcpy(c->d_slots, slots.data(), nslots * sizeof(NameSlot), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(c->d_meta, c->h_meta, ((size_t)n + 1) * sizeof(ContigMeta), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(c->d_blob, blob, (size_t)off[n], cudaMemcpyHostToDevice));
+    c->h_blob = (char *)malloc((size_t)off[n] + 1);
+    c->h_off = (int64_t *)malloc(((size_t)n + 1) * sizeof(int64_t));
+    if (!c->h_blob || !c->h_off) SALSA_FAIL(SALSA_ERR_NOMEM, "out of host memory");
+    memcpy(c->h_blob, blob, (size_t)off[n]);
+    memcpy(c->h_off, off, ((size_t)n + 1) * sizeof(int64_t));
+    delete (std::vector<std::string> *)c->h_involved;
+    c->h_involved = NULL;
     c->n = n;
     c->names_punct = 0;
     for (int64_t i = 0; i < off[n]; i++)
@@ -179,6 +194,14 @@ extern "C" int salsa_avoid_set(salsa_ctx *c, const int32_t *pairs, int32_t npair
     }
     std::sort(keys.begin(), keys.end());
     keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+    {
+        std::vector<std::string> *inv = new std::vector<std::string>();
+        for (int32_t i = 0; i < c->n; i++)
+            if (c->h_meta[i].flags & CTG_INVOLVED) inv->push_back(std::string(c->h_blob + c->h_off[i], (size_t)(c->h_off[i + 1] - c->h_off[i])));
+        std::sort(inv->begin(), inv->end());
+        delete (std::vector<std::string> *)c->h_involved;
+        c->h_involved = inv;
+    }
     if (c->n > 0)
         CUDA_TRY(cudaMemcpy(c->d_meta, c->h_meta, ((size_t)c->n + 1) * sizeof(ContigMeta), cudaMemcpyHostToDevice));
     if (!keys.empty()) {

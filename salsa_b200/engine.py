@@ -173,14 +173,13 @@ class Engine:
             ptr, n = buf.ctypes.data, buf.size
         if nbytes is not None:
             n = nbytes
-        if self.mode != 'dense' or self.navoid:
+        if self.mode != 'dense':
             raise NotImplementedError('host streaming is wired for the dense table only')
         if stage is None:
             stage = torch.empty(2 * chunk_bytes, dtype=torch.uint8, device=self.device)
         chunk_bytes = stage.numel() // 2 // 16 * 16
-        torch.cuda.current_stream().synchronize()
-        check(self.L.salsa_bed_ingest_dense_host(self.ctx, ptr, n, stage.data_ptr(), chunk_bytes,
-                                                 self.table.data_ptr(), self.stats.data_ptr()))
+        check(self.L.salsa_bed_ingest_dense_host(self.ctx, ptr, n, stage.data_ptr(), chunk_bytes, self.table.data_ptr(),
+                                                 self.stats.data_ptr(), torch.cuda.current_stream().cuda_stream))
 
     def ingest_file(self, path, chunk_bytes=256 << 20):
         """Ingest a BED file from disk (what make_links.py does with -b).  The file
@@ -191,7 +190,7 @@ class Engine:
         if size == 0:
             return
         mm = np.memmap(path, dtype=np.uint8, mode='r')
-        if self.mode == 'dense' and not self.navoid:
+        if self.mode == 'dense':
             self.ingest_host(mm, chunk_bytes=min(chunk_bytes, 64 << 20))
             return
         pos = 0

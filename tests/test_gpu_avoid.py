@@ -117,6 +117,22 @@ def test_long_avoid_chains_across_tiles(eng, oracle_lib):
         assert gpu_dict(eng, bed, names, L, avoid) == oracle_dict(oracle_lib, bed, names, L, avoid)
 
 
+def test_host_streaming_with_avoid_list(eng, oracle_lib):
+    """salsa_bed_ingest_dense_host with an avoid set: chunks are cut at lines that can never be skipped."""
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=30, genome=600_000, npairs=12000, seed=78, triple=0.1, noise=0.5)
+    avoid = [(asm.names[i], asm.names[j]) for i, j in ((0, 1), (2, 3), (4, 5), (1, 6), (7, 0), (8, 9), (10, 11))]
+    want = oracle_dict(oracle_lib, bed, asm.names, asm.lengths, avoid)
+    n = asm.ncontig
+    for chunk in (4096, 65536):
+        eng.set_contigs(asm.names, np.asarray(asm.lengths, np.int64), np.ones(n, np.int64), np.ones(n, np.int64), None, avoid)
+        eng.begin_links('dense')
+        eng.ingest_host(np.frombuffer(bed, dtype=np.uint8), chunk_bytes=chunk)
+        eng.stats_read()
+        f, s, e, c = eng.links()
+        assert {(eng.names[a], eng.names[b], int(x)): int(y) for a, b, x, y in zip(f, s, e, c)} == want
+
+
 def test_chunks_start_on_kept_lines(eng, oracle_lib):
     from salsa_b200 import synth
     asm, rec, bed = synth.small_case(ncontig=30, genome=600_000, npairs=8000, seed=77, triple=0.1, noise=0.5)
