@@ -227,7 +227,10 @@ int salsa_sparse_add_segments(const void *d_segments, int32_t nparts, size_t slo
  *   digits : the 12-digit integer D of '%.12g' (sign carried; 0 for x == 0)
  *   exp10  : decimal exponent k of the leading digit (x ~ D * 10^(k-11))
  *   w12    : the double nearest to that decimal, i.e. float(str(x))
- * Exact (320-bit integer arithmetic, round-half-even on the binary value).
+ * Exact (round-half-even on the binary value: 128-bit integers for 1e-8 <= |x| < 1e12, 320-bit ones beyond).
+ * Values that have no digits: x = +inf / -inf / nan give digits = INT64_MIN + 1 / + 2 / + 3 and print as Python
+ * prints them ('inf', '-inf', 'nan'); a finite |x| outside [1e-30, 1e30] gives digits = INT64_MIN, which the
+ * salsa_format_* functions refuse with SALSA_ERR_UNSUPPORTED (the pipeline's own scores cannot get there).
  */
 int salsa_g12(const double *d_x, size_t n, int64_t *d_digits, int32_t *d_exp10, double *d_w12, void *stream);
 

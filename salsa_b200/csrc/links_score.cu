@@ -21,6 +21,12 @@ namespace {
 
 constexpr int NL = 10;   // 32-bit limbs: 320 bits (largest intermediate < 2^250)
 
+// `digits` values that are not digits (include/salsa_b200.h: salsa_g12)
+#define SALSA_G12_RANGE INT64_MIN
+#define SALSA_G12_INF (INT64_MIN + 1)
+#define SALSA_G12_NINF (INT64_MIN + 2)
+#define SALSA_G12_NAN (INT64_MIN + 3)
+
 struct Big {
     uint32_t w[NL];
 };
@@ -174,19 +180,76 @@ __device__ uint64_t g12(double x, int *k10, double *w12)
     return D;
 }
 
+// 10^p, p = 0..19 (each also exactly representable as a double: 5^19 < 2^53)
+__constant__ uint64_t P10[20] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull, 100000000ull,
+                                 1000000000ull, 10000000000ull, 100000000000ull, 1000000000000ull, 10000000000000ull,
+                                 100000000000000ull, 1000000000000000ull, 10000000000000000ull, 100000000000000000ull,
+                                 1000000000000000000ull, 10000000000000000000ull};
+
+// The same result as g12() for 1e-8 <= x < 1e12 (every score and ratio the pipeline produces), in a handful of
+// instructions: with x = m * 2^-s (m < 2^53) and p = 11 - k in 0..19, the integer m * 10^p fits 128 bits, so
+// D = round-half-even(m * 10^p / 2^s) is a shift with an exact look at the bits shifted out; and the double nearest
+// to D / 10^p is ONE IEEE division, because D < 2^53 and 10^p (p <= 22) are both exact doubles (Clinger's fast path).
+__device__ __forceinline__ bool g12_fast(double x, uint64_t *Dout, int *k10, double *w12)
+{
+    if (!(x >= 1e-8 && x < 1e12)) return false;
+    const uint64_t bits = (uint64_t)__double_as_longlong(x);
+    const int be = (int)(bits >> 52);                              // x >= 1e-8: normal
+    const uint64_t m = (bits & 0xFFFFFFFFFFFFFull) | (1ull << 52);
+    const int s = 1075 - be;                                       // x = m * 2^-s, 13 <= s <= 80
+    int k = (int)floor(log10(x));
+    uint64_t D = 0;
+    for (int iter = 0; iter < 3; iter++) {
+        const int p = 11 - k;
+        if (p < 0 || p > 19) return false;
+        const uint64_t T = P10[p];
+        const uint64_t lo = m * T, hi = __umul64hi(m, T);          // m * 10^p, 128 bits
+        uint64_t half, sticky;
+        if (s < 64) {
+            D = (lo >> s) | (hi << (64 - s));
+            if (hi >> s) return false;                             // does not happen (D would exceed 64 bits)
+            half = (lo >> (s - 1)) & 1ull;
+            sticky = lo & ((1ull << (s - 1)) - 1ull);
+        } else if (s == 64) {
+            D = hi;
+            half = lo >> 63;
+            sticky = lo & 0x7FFFFFFFFFFFFFFFull;
+        } else {
+            D = hi >> (s - 64);
+            half = (hi >> (s - 65)) & 1ull;
+            sticky = (hi & ((1ull << (s - 65)) - 1ull)) | lo;
+        }
+        if (D >= 1000000000000ull) { k++; continue; }              // log10 was one off
+        if (D < 100000000000ull) { k--; continue; }
+        if (half && (sticky || (D & 1ull))) D++;                   // round half even on the exact value
+        if (D == 1000000000000ull) { D = 100000000000ull; k++; }
+        *Dout = D;
+        *k10 = k;
+        const int q = k - 11;                                      // D * 10^q -> nearest double
+        *w12 = q <= 0 ? __ddiv_rn((double)D, (double)P10[-q]) : __dmul_rn((double)D, (double)P10[q]);
+        return q >= -19 && q <= 0;
+    }
+    return false;
+}
+
 __device__ __forceinline__ void g12_any(double x, int64_t *digits, int32_t *exp10, double *w12)
 {
-    if (x == 0.0 || !isfinite(x)) {   // 0 prints '0.0'; non-finite values cannot arise from count/norm
+    if (x == 0.0) {                   // prints '0.0'
         *digits = 0; *exp10 = 0; *w12 = x;
         return;
     }
+    if (!isfinite(x)) {               // cannot arise from count/norm; an arbitrary input file can hold them: 'inf', '-inf', 'nan'
+        *digits = isnan(x) ? SALSA_G12_NAN : (x > 0 ? SALSA_G12_INF : SALSA_G12_NINF); *exp10 = 0; *w12 = x;
+        return;
+    }
     double a = fabs(x), w;
-    if (a < 1e-30 || a > 1e30) {      // outside the 320-bit working range: flagged, the host refuses it
-        *digits = INT64_MIN; *exp10 = 0; *w12 = x;
+    if (a < 1e-30 || a > 1e30) {      // outside the 320-bit working range: flagged, the formatters refuse it
+        *digits = SALSA_G12_RANGE; *exp10 = 0; *w12 = x;
         return;
     }
     int k;
-    uint64_t D = g12(a, &k, &w);
+    uint64_t D;
+    if (!g12_fast(a, &D, &k, &w)) D = g12(a, &k, &w);               // the exact 320-bit route covers the rest of the range
     *digits = x < 0 ? -(int64_t)D : (int64_t)D;
     *exp10 = k;
     *w12 = x < 0 ? -w : w;
@@ -226,31 +289,70 @@ __global__ void score_kernel(const uint64_t *keys, const uint64_t *counts, size_
 }
 
 // ---- best-buddy: per-node top-2 with multiplicity ------------------------
-// weights are >= 0, so the IEEE bit pattern orders like the value
-__global__ void node_max_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, unsigned long long *nmax)
+// weights are >= 0, so the IEEE bit pattern orders like the value.
+// The edge list is key-sorted, so the 32 edges of a warp share two or three `u` nodes (one contig, two ends) while their
+// `v` nodes are spread out: the u side is reduced inside the warp first (one atomic per distinct node and warp instead of
+// 32 atomics on the same address), the v side goes straight to the atomics.
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long x)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    unsigned long long b = (unsigned long long)__double_as_longlong(w[i]);
-    atomicMax(&nmax[u[i]], b);          // fast_scaled_scores.py:47-57
-    atomicMax(&nmax[v[i]], b);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        unsigned long long o = __shfl_xor_sync(0xffffffffu, x, d);
+        x = o > x ? o : x;
+    }
+    return x;
 }
 
-__global__ void node_second_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n,
-                                   const unsigned long long *nmax, unsigned long long *nsecond, unsigned int *ntop)
+__global__ void node_max_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, uint32_t nnodes, unsigned long long *nmax)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    unsigned long long b = (unsigned long long)__double_as_longlong(w[i]);
-    int nd[2] = {u[i], v[i]};
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-        if (b == nmax[nd[k]]) atomicAdd(&ntop[nd[k]], 1u);
-        else atomicMax(&nsecond[nd[k]], b);
+    const int lane = threadIdx.x & 31;
+    bool valid = i < n;
+    int un = valid ? u[i] : -1, vn = valid ? v[i] : -1;
+    valid = valid && (uint32_t)un < nnodes && (uint32_t)vn < nnodes;       // ids outside [0, nnodes) touch nothing
+    unsigned long long b = valid ? (unsigned long long)__double_as_longlong(w[i]) : 0ull;
+    if (valid) atomicMax(&nmax[vn], b);          // fast_scaled_scores.py:47-57
+    unsigned act = __ballot_sync(0xffffffffu, valid);
+    while (act) {
+        const int l = __ffs(act) - 1;
+        const int node = __shfl_sync(0xffffffffu, un, l);
+        const bool mine = valid && un == node;
+        const unsigned long long mx = warp_max_u64(mine ? b : 0ull);
+        if (lane == l) atomicMax(&nmax[node], mx);
+        act &= ~__ballot_sync(0xffffffffu, mine);
     }
 }
 
-__global__ void ratio_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, const unsigned long long *nmax,
+__global__ void node_second_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, uint32_t nnodes,
+                                   const unsigned long long *nmax, unsigned long long *nsecond, unsigned int *ntop)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    bool valid = i < n;
+    int un = valid ? u[i] : -1, vn = valid ? v[i] : -1;
+    valid = valid && (uint32_t)un < nnodes && (uint32_t)vn < nnodes;
+    unsigned long long b = valid ? (unsigned long long)__double_as_longlong(w[i]) : 0ull;
+    if (valid) {
+        if (b == nmax[vn]) atomicAdd(&ntop[vn], 1u);
+        else atomicMax(&nsecond[vn], b);
+    }
+    unsigned act = __ballot_sync(0xffffffffu, valid);
+    while (act) {
+        const int l = __ffs(act) - 1;
+        const int node = __shfl_sync(0xffffffffu, un, l);
+        const bool mine = valid && un == node;
+        const unsigned long long top = nmax[node];
+        const unsigned cnt = __popc(__ballot_sync(0xffffffffu, mine && b == top));
+        const unsigned long long sec = warp_max_u64((mine && b != top) ? b : 0ull);
+        if (lane == l) {
+            if (cnt) atomicAdd(&ntop[node], cnt);
+            if (sec) atomicMax(&nsecond[node], sec);
+        }
+        act &= ~__ballot_sync(0xffffffffu, mine);
+    }
+}
+
+__global__ void ratio_kernel(const int32_t *u, const int32_t *v, const double *w, size_t n, uint32_t nnodes, const unsigned long long *nmax,
                              const unsigned long long *nsecond, const unsigned int *ntop, double *best_alt,
                              uint8_t *is_int1, double *ratio, int64_t *digits, int32_t *exp10, int64_t *bdigits,
                              int32_t *bexp10)
@@ -259,6 +361,10 @@ __global__ void ratio_kernel(const int32_t *u, const int32_t *v, const double *w
     if (i >= n) return;
     double wi = w[i];
     int a = u[i], b = v[i];
+    if ((uint32_t)a >= nnodes || (uint32_t)b >= nnodes) {                  // documented precondition violated: a defined, inert result
+        best_alt[i] = 0.0; is_int1[i] = 0; ratio[i] = 0.0; digits[i] = 0; exp10[i] = 0; bdigits[i] = 0; bexp10[i] = 0;
+        return;
+    }
     double mu = __longlong_as_double((long long)nmax[a]), mv = __longlong_as_double((long long)nmax[b]);
     double best = mu > mv ? mu : mv;                       // :79
     if (best == wi) {                                      // :80-82  this edge is the best at both ends
@@ -323,9 +429,9 @@ static int scaled_launch(const int32_t *d_u, const int32_t *d_v, const double *d
     unsigned int *ntop = (unsigned int *)(nsecond + nnodes);
     size_t words = (size_t)nnodes * 2 + ((size_t)nnodes + 1) / 2;
     zero_nodes_kernel<<<nblk(words, 256), 256, 0, st>>>(nmax, words);
-    node_max_kernel<<<nblk(n, 256), 256, 0, st>>>(d_u, d_v, d_w, n, nmax);
-    node_second_kernel<<<nblk(n, 256), 256, 0, st>>>(d_u, d_v, d_w, n, nmax, nsecond, ntop);
-    ratio_kernel<<<nblk(n, 128), 128, 0, st>>>(d_u, d_v, d_w, n, nmax, nsecond, ntop, d_best_alt, d_is_int1, d_ratio,
+    node_max_kernel<<<nblk(n, 256), 256, 0, st>>>(d_u, d_v, d_w, n, (uint32_t)nnodes, nmax);
+    node_second_kernel<<<nblk(n, 256), 256, 0, st>>>(d_u, d_v, d_w, n, (uint32_t)nnodes, nmax, nsecond, ntop);
+    ratio_kernel<<<nblk(n, 128), 128, 0, st>>>(d_u, d_v, d_w, n, (uint32_t)nnodes, nmax, nsecond, ntop, d_best_alt, d_is_int1, d_ratio,
                                                d_digits, d_exp10, d_bdigits, d_bexp10);
     CUDA_TRY(cudaGetLastError());
     return SALSA_OK;
@@ -407,6 +513,10 @@ static int fmt_g12(int64_t digits, int32_t k, char *out)
 {
     char *p = out;
     if (digits == 0) { memcpy(p, "0.0", 3); return 3; }
+    if (digits == SALSA_G12_INF) { memcpy(p, "inf", 3); return 3; }          // Python-2 str(float('inf'))
+    if (digits == SALSA_G12_NINF) { memcpy(p, "-inf", 4); return 4; }
+    if (digits == SALSA_G12_NAN) { memcpy(p, "nan", 3); return 3; }
+    if (digits == SALSA_G12_RANGE) return -1;                                 // |x| outside [1e-30, 1e30]: no digits were computed
     if (digits < 0) { *p++ = '-'; digits = -digits; }
     char d[16];
     int nd = 12;
@@ -454,7 +564,9 @@ extern "C" int salsa_format_g12(const int64_t *h_digits, const int32_t *h_exp10,
     for (size_t i = 0; i < n; i++) {
         if (pos + 32 > out_cap) SALSA_FAIL(SALSA_ERR_ARG, "salsa_format_g12: output buffer too small");
         h_off[i] = (int64_t)pos;
-        pos += (size_t)fmt_g12(h_digits[i], h_exp10[i], h_out + pos);
+        int len = fmt_g12(h_digits[i], h_exp10[i], h_out + pos);
+        if (len < 0) SALSA_FAIL(SALSA_ERR_UNSUPPORTED, "salsa_format_g12: value %zu lies outside [1e-30, 1e30]", i);
+        pos += (size_t)len;
     }
     h_off[n] = (int64_t)pos;
     return SALSA_OK;
@@ -476,7 +588,11 @@ extern "C" int64_t salsa_format_links(const char *names_blob, const int64_t *nam
         memcpy(p, names_blob + name_off[b], lb); p += lb;
         *p++ = ':'; *p++ = (ends[i] & 1) ? 'E' : 'B'; *p++ = '\t';
         if (is_int0[i]) *p++ = '0';
-        else p += fmt_g12(digits[i], exp10[i], p);
+        else {
+            int len = fmt_g12(digits[i], exp10[i], p);
+            if (len < 0) { salsa_set_error("salsa_format_links: score %zu lies outside [1e-30, 1e30]", i); return -1; }
+            p += len;
+        }
         *p++ = '\t';
         p = put_i64(p, count[i]);
         *p++ = '\n';
@@ -498,11 +614,14 @@ extern "C" int64_t salsa_format_scaled(const char *node_blob, const int64_t *nod
         if ((size_t)(p - out) + la + lb + 140 > out_cap) { salsa_set_error("salsa_format_scaled: buffer too small"); return -1; }
         memcpy(p, node_blob + node_off[a], la); p += la; *p++ = '\t';
         memcpy(p, node_blob + node_off[b], lb); p += lb; *p++ = '\t';
-        p += fmt_g12(w_digits[i], w_exp10[i], p); *p++ = '\t';
-        if (b_is_int1[i]) *p++ = '1';
-        else p += fmt_g12(b_digits[i], b_exp10[i], p);
-        *p++ = '\t';
-        p += fmt_g12(r_digits[i], r_exp10[i], p); *p++ = '\t';
+        int l1 = fmt_g12(w_digits[i], w_exp10[i], p);
+        if (l1 >= 0) { p += l1; *p++ = '\t'; }
+        int l2 = b_is_int1[i] ? 1 : fmt_g12(b_digits[i], b_exp10[i], p);
+        if (b_is_int1[i]) *p = '1';
+        if (l2 >= 0) { p += l2; *p++ = '\t'; }
+        int l3 = fmt_g12(r_digits[i], r_exp10[i], p);
+        if (l1 < 0 || l2 < 0 || l3 < 0) { salsa_set_error("salsa_format_scaled: a value of edge %zu lies outside [1e-30, 1e30]", i); return -1; }
+        p += l3; *p++ = '\t';
         p = put_i64(p, links[i]);
         memcpy(p, "\tFalse\tFalse\n", 13); p += 13;
     }

@@ -41,6 +41,10 @@ def test_g12_matches_python2_str(eng, oracle_lib):
            3 / 14.0, 123456789012.0, 1234567890123.0, 0.0001, 0.00001, 9.9999999999995e-5, 1e22, 3e-29, 7e29,
            0.0, -2.5, -1 / 3.0]
     xs += [c / (a * 0.5 + b * 0.5) for a, b, c in rng.integers(1, 5000, (50000, 3))]
+    # the edges of the 128-bit fast path (1e-8 <= x < 1e12) and exact ties of its rounding step
+    xs += [1e-8, 1e-8 * (1 - 2 ** -53), 1e-8 * (1 + 2 ** -52), 9.99999999999e-9, 1e12, 1e12 * (1 - 2 ** -53), 999999999999.75,
+           0.5 + 2.0 ** -40, 1.0 + 2.0 ** -36, 2.0 ** -20, 2.0 ** 39 + 0.5, 2.0 ** 38 + 0.5, 1e-29, 1e29]
+    xs += [float(m) / 8.0 + 1e5 for m in range(0, 64)] + [(2 * m + 1) / 2.0 ** 14 for m in range(40)]
     x = np.array(xs, dtype=np.float64)
     d, k, w = eng.g12(x)
     txt = fmt(eng, d, k)
@@ -53,6 +57,23 @@ def test_g12_matches_python2_str(eng, oracle_lib):
     want_all = [s if ('.' in s or 'e' in s or 'n' in s) else s + '.0' for s in want_all]
     assert txt == want_all
     assert (w == np.array([float(s) for s in want_all])).all()
+
+
+def test_g12_values_without_digits(eng):
+    """inf / nan print as Python prints them; a finite value outside [1e-30, 1e30] is refused by the formatters instead
+    of being printed wrongly (the pipeline's own scores never get there; an arbitrary contig_links file can)."""
+    import ctypes as C
+    x = np.array([float('inf'), float('-inf'), float('nan'), 2.5], dtype=np.float64)
+    d, k, w = eng.g12(x)
+    assert fmt(eng, d, k) == ['inf', '-inf', 'nan', '2.5']
+    assert np.isinf(w[0]) and np.isinf(w[1]) and np.isnan(w[2]) and w[3] == 2.5
+    for bad in (1e-31, 1e31, 5e-324, -3e200):
+        d, k, w = eng.g12(np.array([1.5, bad]))
+        assert d[1] == np.iinfo(np.int64).min and w[1] == bad
+        out = C.create_string_buffer(128)
+        off = np.zeros(3, np.int64)
+        rc = eng.L.salsa_format_g12(np.ascontiguousarray(d).ctypes.data, np.ascontiguousarray(k).ctypes.data, 2, out, 128, off.ctypes.data)
+        assert rc != 0 and b'1e-30' in eng.L.salsa_last_error()
 
 
 def _case(seed, ncontig=40, npairs=20000):

@@ -8,7 +8,10 @@ variant, whose working arrays live inside the library image.  This test calls
 it through the C ABI and requires bit-identical results to the ordinary entry
 point (which takes a caller-provided scratch buffer), twice in a row -- the
 second call runs over whatever the first left in the shared array, with a
-different, smaller graph, so stale contents would show.
+different, smaller graph, so stale contents would show.  The results are also
+held to the CPU oracle's restatement of fast_scaled_scores.py, and the free
+device memory is read before and after the call: the `_static` variant must not
+take a byte.
 
 The file name sorts last on purpose: a run that stops at the first failure has
 then already executed every other test.
@@ -36,7 +39,7 @@ def _graph(seed, nnodes, nedges):
     return np.array(u, np.int32), np.array(v, np.int32), w.astype(np.float64)
 
 
-def _run(L, torch, static, u, v, w, nnodes):
+def _run(L, torch, static, u, v, w, nnodes, alloc_probe=None):
     dev = torch.device('cuda', 0)
     du, dv, dw = (torch.from_numpy(a).to(dev) for a in (u, v, w))
     n = len(u)
@@ -47,7 +50,12 @@ def _run(L, torch, static, u, v, w, nnodes):
     st = torch.cuda.current_stream().cuda_stream
     o = [outs[k].data_ptr() for k in ('best', 'int1', 'ratio', 'rd', 'rk', 'bd', 'bk')]
     if static:
+        torch.cuda.synchronize()
+        free0 = torch.cuda.mem_get_info(dev)[0]            # cudaMemGetInfo: the driver's view, below torch's cache
         rc = L.salsa_scaled_scores_static(du.data_ptr(), dv.data_ptr(), dw.data_ptr(), n, nnodes, *o, st)
+        torch.cuda.synchronize()
+        if alloc_probe is not None:
+            alloc_probe.append(free0 - torch.cuda.mem_get_info(dev)[0])
     else:
         scratch = torch.full((L.salsa_scaled_scratch_bytes(nnodes) // 8 + 1,), 0x5A5A5A5A, dtype=torch.int64, device=dev)
         rc = L.salsa_scaled_scores(du.data_ptr(), dv.data_ptr(), dw.data_ptr(), n, nnodes, scratch.data_ptr(), *o, st)
@@ -68,13 +76,30 @@ def test_static_scratch_matches_caller_scratch_twice():
     for seed, nnodes, nedges in ((1, 60000, 200000), (2, 500, 3000)):
         u, v, w = _graph(seed, nnodes, nedges)
         want = _run(L, torch, False, u, v, w, nnodes)
-        got = _run(L, torch, True, u, v, w, nnodes)
+        taken = []
+        if seed == 1:
+            _run(L, torch, True, u, v, w, nnodes)              # the one-time address look-up happens in the first call
+        got = _run(L, torch, True, u, v, w, nnodes, alloc_probe=taken)
+        assert taken == [0], 'the _static entry point took device memory: %r bytes' % taken
         for k in want:
             assert np.array_equal(got[k], want[k]), k          # bit-exact, like every other parity test here
         assert (got['ratio'] >= 0).all() and set(np.unique(got['int1'])) <= {0, 1}
+        # and against the CPU oracle (fast_scaled_scores.py:13-33,47-57,79-86)
+        import oracle
+        ob, oi, orat = oracle.scaled_scores(u, v, w, nnodes)
+        assert np.array_equal(got['best'], ob) and np.array_equal(got['int1'], oi) and np.array_equal(got['ratio'], orat)
     # beyond the limit: refused with a message that names it, nothing launched
     u, v, w = _graph(3, 100, 50)
     dev = torch.device('cuda', 0)
     z = torch.zeros(64, dtype=torch.int64, device=dev)
     rc = L.salsa_scaled_scores_static(z.data_ptr(), z.data_ptr(), z.data_ptr(), 50, limit + 1, *([z.data_ptr()] * 7), None)
     assert rc != 0 and b'65536' in L.salsa_last_error()
+    # node ids outside [0, nnodes) -- a violated precondition -- must not reach beyond the built-in array: the edge is
+    # ignored and gets an inert result, the other edges are unaffected
+    u, v, w = _graph(4, 300, 900)
+    want = _run(L, torch, True, u, v, w, 300)
+    u2, v2, w2 = np.append(u, [7, 300000]).astype(np.int32), np.append(v, [-5, 3]).astype(np.int32), np.append(w, [99.0, 98.0])
+    got = _run(L, torch, True, u2, v2, w2, 300)
+    for k in want:
+        assert np.array_equal(got[k][:900], want[k]), k
+    assert (got['ratio'][900:] == 0).all()
