@@ -232,21 +232,30 @@ __device__ __forceinline__ uint32_t cheap16_of(const uint4 &v)
 struct CheapTest { static constexpr bool value = true; };
 struct ExactTest { static constexpr bool value = false; };
 
-constexpr int SAMPLE_WIN = 65536;
+constexpr int SAMPLE_WIN = 16384;      // bytes per window; three windows: start, middle, end of the text
 __global__ void __launch_bounds__(256) bed_sample_kernel(ScanArgs A, int names_punct, int *d_mode)
 {
     __shared__ unsigned int cnt[2];            // newlines, bytes in 0x21..0x2E
     if (threadIdx.x < 2) cnt[threadIdx.x] = 0;
     __syncthreads();
-    const unsigned long long n = A.dend - A.mis;
+    const unsigned long long n16 = A.dend & ~15ull;          // whole 16-byte granules of [abase, abase + dend)
     unsigned int nl = 0, pu = 0;
     for (int w = 0; w < 3; w++) {
-        unsigned long long b = w == 0 ? 0ull : (w == 1 ? n / 2 : (n > (unsigned long long)SAMPLE_WIN ? n - SAMPLE_WIN : 0ull));
-        if (w > 0 && n <= (unsigned long long)SAMPLE_WIN) break;
-        for (unsigned long long i = b + threadIdx.x; i < b + SAMPLE_WIN && i < n; i += 256) {
-            const uint32_t c = A.abase[A.mis + i];
-            nl += c == 10u;
-            pu += (c - 0x21u) <= 0x0Du;
+        unsigned long long b = w == 0 ? 0ull : (w == 1 ? (n16 / 2) & ~15ull : (n16 > (unsigned long long)SAMPLE_WIN ? n16 - SAMPLE_WIN : 0ull));
+        if (w > 0 && n16 <= (unsigned long long)SAMPLE_WIN) break;
+        for (unsigned long long i = b + 16ull * threadIdx.x; i < b + SAMPLE_WIN && i < n16; i += 16ull * 256) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(A.abase + i));
+            const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const uint32_t c = (ws[k] >> (8 * q)) & 255u;
+                    if (i + 4 * k + q < A.mis) continue;      // bytes before the caller's pointer are not text
+                    nl += c == 10u;
+                    pu += (c - 0x21u) <= 0x0Du;
+                }
+            }
         }
     }
     atomicAdd(&cnt[0], nl);
