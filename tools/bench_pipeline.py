@@ -39,24 +39,33 @@ def run(bin_dir, data, out, extra):
 
 def main():
     pairs = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
-    d = tempfile.mkdtemp()
+    d = tempfile.mkdtemp(dir=os.environ.get('SALSA_BENCH_TMP'))
     data = d + '/data'
-    pu.write_dataset(data, ncontig=200, genome=2_000_000, len_lo=2_000, len_hi=40_000, npairs=pairs, seed=20261107, nchrom=4)
-    import oracle
-    oracle.build()
-    obin = pu.make_oracle_bin(d + '/obin')
-    args = ['-e', 'GATC', '-i', '3', '-m', 'no']
+    if '--cfg2' in sys.argv:
+        # BASELINE configs[1]'s assembly: 3.1 Gb in 3,000 contigs, -e GATC,GANTC (the BED holds `pairs` pairs)
+        t0 = time.time()
+        pu.write_dataset(data, ncontig=3000, genome=3_100_000_000, len_lo=50_000, len_hi=20_000_000, npairs=pairs, seed=20261108, nchrom=23)
+        sys.stderr.write('data set written in %.1f s\n' % (time.time() - t0))
+        args = ['-e', 'GATC,GANTC', '-i', '3', '-m', 'yes' if '--misasm' in sys.argv else 'no']
+        shape = 'BASELINE configs[1] assembly: 3.1 Gb, 3,000 contigs, %d pairs, %s' % (pairs, ' '.join(args))
+    else:
+        pu.write_dataset(data, ncontig=200, genome=2_000_000, len_lo=2_000, len_hi=40_000, npairs=pairs, seed=20261107, nchrom=4)
+        args = ['-e', 'GATC', '-i', '3', '-m', 'no']
+        shape = 'BASELINE configs[0]: 2 Mb genome, 200 contigs, %d pairs, %s' % (pairs, ' '.join(args))
     wg, sg, ig = run(pu.BIN, data, d + '/gpu', args)
     if '--gpu-only' in sys.argv:
-        print(json.dumps({'metric': 'seconds_per_pipeline_iteration', 'pairs': pairs, 'iterations_run': ig,
+        print(json.dumps({'metric': 'seconds_per_pipeline_iteration', 'config': shape, 'pairs': pairs, 'iterations_run': ig,
                           'gpu_path': {'wall_s': wg, 'startup_s': sg.get('startup', 0.0),
                                        's_per_iteration_after_startup': (sum(sg.values()) - sg.get('startup', 0.0)) / ig, 'steps_s': sg}}))
         return
+    import oracle
+    oracle.build()
+    obin = pu.make_oracle_bin(d + '/obin')
     wo, so, io = run(obin, data, d + '/cpu', args)
     same = open(d + '/gpu/scaffolds_FINAL.agp').read() == open(d + '/cpu/scaffolds_FINAL.agp').read()
     hot = ('make_links.py', 'fast_scaled_scores.py', 'RE_sites.py', 'break_contigs', 'break_contigs_start')
     print(json.dumps({
-        'metric': 'seconds_per_pipeline_iteration', 'config': 'BASELINE configs[0]: 2 Mb genome, 200 contigs, %d pairs, -e GATC -i 3 -m no' % pairs,
+        'metric': 'seconds_per_pipeline_iteration', 'config': shape,
         'iterations_run': ig, 'identical_final_agp': same,
         'gpu_path': {'wall_s': wg, 's_per_iteration': wg / ig, 'startup_s': sg.get('startup', 0.0),
                      's_per_iteration_after_startup': (sum(sg.values()) - sg.get('startup', 0.0)) / ig,
