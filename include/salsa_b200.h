@@ -70,6 +70,13 @@ void salsa_ctx_destroy(salsa_ctx *ctx);
  * lines whose first four fields hold one of the 14 characters 0x21..0x2E take the slow full parser.  mode 0 (default):
  * a sample of the text decides per call; 1: always exact; 2: always the superset. */
 int salsa_ctx_scan_mode(salsa_ctx *ctx, int mode);
+/* Device timers (the reference itself has no timers: run_pipeline.py only logs commands).
+ * After salsa_timers_enable(ctx, 1) every BED link scan launched through this context is bracketed by a pair of CUDA
+ * events on its stream.  salsa_timers waits for the events recorded so far and reports accumulated milliseconds and
+ * launch counts: slot 0 = BED link scans (salsa_bed_ingest_*); slots 1..3 are reserved and read 0.  n = number of
+ * slots to write; reset != 0 clears the accumulators afterwards.  Synchronises on the recorded events only. */
+int salsa_timers_enable(salsa_ctx *ctx, int on);
+int salsa_timers(salsa_ctx *ctx, double *h_out_ms, uint64_t *h_out_launches, int32_t n, int reset);
 
 /*
  * Contig table: replaces the three host dicts of make_links.py:37-48

@@ -44,6 +44,8 @@ SIGNATURES = {
     'salsa_ctx_create': (C.c_int, [C.c_int, C.POINTER(c_void_p)]),
     'salsa_ctx_destroy': (None, [c_void_p]),
     'salsa_ctx_scan_mode': (C.c_int, [c_void_p, C.c_int]),
+    'salsa_timers_enable': (C.c_int, [c_void_p, C.c_int]),
+    'salsa_timers': (C.c_int, [c_void_p, c_void_p, c_void_p, c_i32, C.c_int]),
     'salsa_names_build': (C.c_int, [c_void_p, C.c_char_p, c_void_p, c_i32, c_void_p, c_void_p]),
     'salsa_names_count': (c_i32, [c_void_p]),
     'salsa_avoid_set': (C.c_int, [c_void_p, c_void_p, c_i32]),

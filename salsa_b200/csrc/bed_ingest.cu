@@ -120,12 +120,18 @@ template <bool SPARSE>
 static int scan_links(const LinkArgs &L, salsa_ctx *ctx, const void *d_bed, size_t nbytes, uint64_t base_offset, uint64_t *d_stats,
                       cudaStream_t st)
 {
+    void *slot = NULL;
+    int rc = salsa_timer_begin(ctx, st, &slot);            // salsa_timers: no-ops unless enabled
+    if (rc) return rc;
     if (ctx->t.navoid > 0)
-        return bedscan::launch_scan<LinkPolicy<SPARSE, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
-    if (use_tile_scanner())
-        return bedscan::launch_scan<LinkPolicy<SPARSE, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
-    return bedstream::launch_stream<LinkEmit<SPARSE>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, ctx->scan_mode, ctx->names_punct,
-                                                      ctx->d_mode, st);
+        rc = bedscan::launch_scan<LinkPolicy<SPARSE, true>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
+    else if (use_tile_scanner())
+        rc = bedscan::launch_scan<LinkPolicy<SPARSE, false>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, st);
+    else
+        rc = bedstream::launch_stream<LinkEmit<SPARSE>>(L, ctx->t, d_bed, nbytes, base_offset, d_stats, ctx->scan_mode, ctx->names_punct,
+                                                        ctx->d_mode, st);
+    salsa_timer_end(ctx, st, slot);
+    return rc;
 }
 
 __global__ void stats_reset_kernel(uint64_t *s)

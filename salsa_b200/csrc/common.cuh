@@ -73,7 +73,14 @@ struct salsa_ctx {
     int64_t *h_off;
     void *h_involved;          // std::vector<std::string> *
     cudaEvent_t ev_user;       // orders the internal streams after the caller's stream
+    // salsa_timers: when enabled, every BED scan launch is bracketed by a pair of events
+    int timing;
+    void *timer_events;        // std::vector<std::pair<cudaEvent_t, cudaEvent_t>> *
+    double timer_ms[4];        // accumulated: [0] BED scan kernels
+    uint64_t timer_n[4];
 };
+int salsa_timer_begin(salsa_ctx *c, cudaStream_t st, void **slot);
+void salsa_timer_end(salsa_ctx *c, cudaStream_t st, void *slot);
 int salsa_ctx_streams(salsa_ctx *c);
 
 __host__ __device__ inline uint32_t salsa_rotl(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }

@@ -4,9 +4,12 @@
 
 #include <algorithm>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "common.cuh"
+
+typedef std::vector<std::pair<cudaEvent_t, cudaEvent_t> > EventPairs;      // salsa_timers
 
 static thread_local char g_err[512] = "";
 
@@ -69,6 +72,11 @@ extern "C" void salsa_ctx_destroy(salsa_ctx *c)
     cudaFree(c->d_avoid);
     cudaFree(c->d_mode);
     delete (std::vector<std::string> *)c->h_involved;
+    if (c->timer_events) {
+        EventPairs *v = (EventPairs *)c->timer_events;
+        for (size_t i = 0; i < v->size(); i++) { cudaEventDestroy((*v)[i].first); cudaEventDestroy((*v)[i].second); }
+        delete v;
+    }
     if (c->streams_ready) {
         cudaEventDestroy(c->ev_user);
         cudaStreamDestroy(c->s_copy);
@@ -93,6 +101,62 @@ int salsa_ctx_streams(salsa_ctx *c)
 }
 
 extern "C" int32_t salsa_names_count(const salsa_ctx *c) { return c ? c->n : 0; }
+
+// ---- timers (the reference has none; the driver's timings.tsv is per process) ----
+int salsa_timer_begin(salsa_ctx *c, cudaStream_t st, void **slot)
+{
+    *slot = NULL;
+    if (!c->timing) return SALSA_OK;
+    if (!c->timer_events) c->timer_events = new EventPairs();
+    cudaEvent_t a, b;
+    CUDA_TRY(cudaEventCreate(&a));
+    CUDA_TRY(cudaEventCreate(&b));
+    CUDA_TRY(cudaEventRecord(a, st));
+    EventPairs *v = (EventPairs *)c->timer_events;
+    v->push_back(std::make_pair(a, b));
+    *slot = (void *)(uintptr_t)v->size();          // index + 1
+    return SALSA_OK;
+}
+
+void salsa_timer_end(salsa_ctx *c, cudaStream_t st, void *slot)
+{
+    if (!slot) return;
+    EventPairs *v = (EventPairs *)c->timer_events;
+    cudaEventRecord((*v)[(size_t)(uintptr_t)slot - 1].second, st);
+}
+
+extern "C" int salsa_timers_enable(salsa_ctx *c, int on)
+{
+    if (!c) SALSA_FAIL(SALSA_ERR_ARG, "salsa_timers_enable: ctx is NULL");
+    c->timing = on ? 1 : 0;
+    return SALSA_OK;
+}
+
+extern "C" int salsa_timers(salsa_ctx *c, double *out_ms, uint64_t *out_launches, int32_t n, int reset)
+{
+    if (!c || !out_ms || n < 1) SALSA_FAIL(SALSA_ERR_ARG, "salsa_timers: bad argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    EventPairs *v = (EventPairs *)c->timer_events;
+    if (v) {
+        for (size_t i = 0; i < v->size(); i++) {
+            CUDA_TRY(cudaEventSynchronize((*v)[i].second));
+            float ms = 0;
+            CUDA_TRY(cudaEventElapsedTime(&ms, (*v)[i].first, (*v)[i].second));
+            c->timer_ms[0] += ms;
+            c->timer_n[0]++;
+            cudaEventDestroy((*v)[i].first);
+            cudaEventDestroy((*v)[i].second);
+        }
+        v->clear();
+    }
+    for (int32_t i = 0; i < n; i++) {
+        out_ms[i] = i < 4 ? c->timer_ms[i] : 0.0;
+        if (out_launches) out_launches[i] = i < 4 ? c->timer_n[i] : 0;
+    }
+    if (reset)
+        for (int i = 0; i < 4; i++) { c->timer_ms[i] = 0; c->timer_n[i] = 0; }
+    return SALSA_OK;
+}
 
 extern "C" int salsa_ctx_scan_mode(salsa_ctx *c, int mode)
 {

@@ -58,6 +58,16 @@ class Engine:
         superset.  Results never depend on it (include/salsa_b200.h: salsa_ctx_scan_mode)."""
         check(self.L.salsa_ctx_scan_mode(self.ctx, int(mode)))
 
+    def timers(self, enable=None, reset=False):
+        """Device time of the BED link scans launched through this engine (salsa_timers): (ms, launches).
+        timers(enable=True) switches the event bracketing on first."""
+        if enable is not None:
+            check(self.L.salsa_timers_enable(self.ctx, 1 if enable else 0))
+        ms = (C.c_double * 4)()
+        nl = (C.c_uint64 * 4)()
+        check(self.L.salsa_timers(self.ctx, ms, nl, 4, 1 if reset else 0))
+        return float(ms[0]), int(nl[0])
+
     def close(self):
         if self.ctx:
             self.L.salsa_ctx_destroy(self.ctx)
@@ -237,12 +247,13 @@ class Engine:
             kptr = keys.data_ptr()
         scratch = torch.empty(self.L.salsa_links_compact_scratch_bytes(ncell) // 8 + 1, dtype=torch.int64, device=self.device)
         n = C.c_uint64(0)
-        check(self.L.salsa_links_compact(kptr, cnt.data_ptr(), ncell, None, None, 0, scratch.data_ptr(), C.byref(n), st))
-        m = n.value
-        ok = torch.empty(max(m, 1), dtype=torch.int64, device=self.device)
-        oc = torch.empty(max(m, 1), dtype=torch.int64, device=self.device)
-        check(self.L.salsa_links_compact(kptr, cnt.data_ptr(), ncell, ok.data_ptr(), oc.data_ptr(), m, scratch.data_ptr(),
+        # one pass: there are at most as many links as counted pairs (and as cells)
+        bound = min(ncell, self.stats_read(raise_on_error=False).pairs)
+        ok = torch.empty(max(bound, 1), dtype=torch.int64, device=self.device)
+        oc = torch.empty(max(bound, 1), dtype=torch.int64, device=self.device)
+        check(self.L.salsa_links_compact(kptr, cnt.data_ptr(), ncell, ok.data_ptr(), oc.data_ptr(), bound, scratch.data_ptr(),
                                          C.byref(n), st))
+        m = n.value
         if self.mode != 'dense' and m:
             ok2, oc2 = torch.empty_like(ok), torch.empty_like(oc)
             tb = C.c_size_t(0)

@@ -6,7 +6,7 @@ optional second AGP maps `_1`/`_2` pieces back to the pre-cleaning names and coo
 import pickle
 import re
 
-from .clean import read_fasta
+from .clean import read_fasta, wrap_fasta
 
 _COMP = {'A': 'T', 'B': 'N', 'C': 'G', 'G': 'C', 'T': 'A', 'N': 'N', 'R': 'N', 'M': 'N', 'Y': 'N', 'S': 'N', 'W': 'N', 'K': 'N',
          'V': 'N', 'H': 'N', 'D': 'N', 'a': 't', 'c': 'g', 'g': 'c', 't': 'a', 'n': 'n', ' ': ''}
@@ -15,10 +15,13 @@ _COMP = {'A': 'T', 'B': 'N', 'C': 'G', 'G': 'C', 'T': 'A', 'N': 'N', 'R': 'N', '
 _TABLE = str.maketrans(_COMP)
 
 
+_KNOWN = ''.join(_COMP.keys()).encode('latin-1')
+
+
 def revcomp(s):
-    bad = set(s) - _COMP.keys()
+    bad = s.encode('latin-1', 'replace').translate(None, _KNOWN)       # what is left is outside the table
     if bad:
-        raise KeyError(min(bad))                   # the reference's table lookup raises on other characters
+        raise KeyError(min(set(s) - _COMP.keys()))                     # the reference's table lookup raises on other characters
     return s.translate(_TABLE)[::-1]
 
 
@@ -48,7 +51,7 @@ def write_outputs(cleaned, scaffold_map_path, fasta_out, agp_out, breaks_path=No
     total = {s: sum(clen[p[i].split(':')[0]] for i in range(0, len(p) - 1, 2)) for s, p in scaff_map.items()}
     ranked = sorted(total.items(), key=lambda kv: kv[1], reverse=True)        # stable: ties keep map order
     orig = open(agp_orig_out, 'w') if agp_orig_out else None
-    with open(agp_out, 'w') as agp, open(fasta_out, 'w') as fa:
+    with open(agp_out, 'w') as agp, open(fasta_out, 'wb') as fa:
         for cid, (key, _) in enumerate(ranked, 1):
             path = scaff_map[key]
             start, comp, parts = 1, 1, []
@@ -78,9 +81,7 @@ def write_outputs(cleaned, scaffold_map_path, fasta_out, agp_out, breaks_path=No
                     if orig:
                         orig.write(gap)
                     start, comp = end + 1, comp + 1
-            s = ''.join(parts)
-            fa.write('>scaffold_%d\n' % cid)
-            for i in range(0, len(s), 80):
-                fa.write(s[i:i + 80] + '\n')
+            fa.write(b'>scaffold_%d\n' % cid)
+            fa.write(wrap_fasta(''.join(parts)))
     if orig:
         orig.close()

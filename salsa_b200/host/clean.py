@@ -7,8 +7,10 @@ without a last write), so the cleaned BED holds floor(n / 1e6) * 1e6 lines.
 """
 
 
-def read_fasta(path):
-    """name -> sequence (lines rstripped and joined), later duplicate wins (correct.py:4-19)."""
+import numpy as np
+
+
+def _read_fasta_lines(path):
     fa, cur = {}, None
     with open(path, 'r', encoding='latin-1', newline='\n') as fh:
         for ln in fh:
@@ -18,6 +20,43 @@ def read_fasta(path):
             else:
                 fa[cur].append(ln.rstrip())
     return {k: ''.join(v) for k, v in fa.items()}
+
+
+def read_fasta(path):
+    """name -> sequence (lines rstripped and joined), later duplicate wins (correct.py:4-19).
+    Whole records at a time (a 3 Gb assembly has 50 million lines); anything unusual -- text before the first
+    header, whitespace other than the newlines inside a record -- goes through the line loop, which is the
+    reference's own and raises what it raises."""
+    with open(path, 'rb') as fh:
+        data = fh.read()
+    if not data:
+        return {}
+    if data[:1] != b'>':
+        return _read_fasta_lines(path)
+    a = np.frombuffer(data, dtype=np.uint8)
+    starts = np.concatenate(([0], np.flatnonzero((a[1:] == 62) & (a[:-1] == 10)) + 1)).tolist()
+    starts.append(len(data))
+    fa = {}
+    for b, e in zip(starts[:-1], starts[1:]):
+        nl = data.find(b'\n', b, e)
+        head = data[b + 1:nl if nl >= 0 else e]
+        body = data[nl + 1:e] if nl >= 0 else b''
+        if not head.split() or any(c in body for c in (b' ', b'\t', b'\r', b'\x0b', b'\x0c')) or b'\r' in head:
+            return _read_fasta_lines(path)
+        fa[head.decode('latin-1').rstrip().split()[0]] = body.translate(None, b'\n').decode('latin-1')
+    return fa
+
+
+def wrap_fasta(s, width=80):
+    """The sequence in lines of `width` characters, every line (the last, shorter one too) ending in a newline: what
+    `for i in range(0, len(s), width): write(s[i:i + width] + '\\n')` writes, as one bytes object."""
+    b = s.encode('latin-1')
+    k = len(b) // width
+    out = np.empty((k, width + 1), np.uint8)
+    out[:, :width] = np.frombuffer(b, dtype=np.uint8, count=k * width).reshape(k, width)
+    out[:, width] = 10
+    tail = b[k * width:]
+    return out.tobytes() + (tail + b'\n' if tail else b'')
 
 
 def clean(assembly, breaks_path, bed, outdir, flush_every=1000000):
@@ -53,11 +92,10 @@ def clean(assembly, breaks_path, bed, outdir, flush_every=1000000):
                 out.writelines(buf)
                 buf = []
         # (no final flush: see module docstring)
-    with open(outdir + '/asm.cleaned.fasta', 'w') as fo:
+    with open(outdir + '/asm.cleaned.fasta', 'wb') as fo:
         for name, s in new_seq.items():
-            fo.write('>' + name + '\n')
-            for i in range(0, len(s), 80):
-                fo.write(s[i:i + 80] + '\n')
+            fo.write(('>' + name + '\n').encode('latin-1'))
+            fo.write(wrap_fasta(s))
     with open(outdir + '/scaffold_length_iteration_1', 'w') as fo:
         for name, s in new_seq.items():
             fo.write('%s\t%d\n' % (name, len(s)))

@@ -176,6 +176,24 @@ def test_sparse_table_grows_like_the_reference_dict(eng, oracle_lib):
     assert got == want and sum(got.values()) == st.pairs
 
 
+def test_timers_through_the_abi(eng):
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=30, genome=600_000, npairs=20000, seed=5)
+    n = asm.ncontig
+    eng.set_contigs(asm.names, np.asarray(asm.lengths, np.int64), np.ones(n, np.int64), np.ones(n, np.int64))
+    dev_bed = torch.frombuffer(bytearray(bed), dtype=torch.uint8).to(eng.device)
+    eng.timers(enable=True, reset=True)
+    eng.begin_links('dense')
+    for _ in range(3):
+        eng.ingest_device(dev_bed)
+    ms, launches = eng.timers(reset=True)
+    assert launches == 3 and 0 < ms < 1000
+    eng.timers(enable=False)
+    eng.ingest_device(dev_bed)
+    assert eng.timers() == (0.0, 0)
+    eng.stats_read()
+
+
 def test_empty_and_tiny(eng, oracle_lib):
     names, L = [b'A', b'B'], [1000, 2000]
     for bed in (b'', b'\n', b'A 1 2 r/1', b'A 1 2 r/1\n', b'A 100 200 r1/1\nB 1900 1990 r1/2\n', b'A 100 200 r1/1\nB 1900 1990 r1/2'):
