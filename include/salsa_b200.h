@@ -357,6 +357,21 @@ int salsa_re_count(const uint64_t *d_planes, const uint64_t *d_blk_off, const ui
                    uint64_t *d_occ_scratch, void *stream);
 
 /*
+ * RE counts of the scaffolds of iterations >= 2.  Replaces layout_unitigs.py:736-814 and refactor_breaks.py:63-131:
+ * the contigs of a scaffold lie end to end; contigs wholly left / right of the midpoint (integer length/2) give all
+ * their sites to that side, the contig(s) touching the midpoint are split in proportion
+ * (float(left+right)/len * part, summed in path order in double precision, int() at the end); a single-contig
+ * scaffold keeps (left, right) of its contig, swapped when it is reversed.
+ *   d_path_off[nscaf+1], d_path_contig : the contigs of each scaffold in path order (CSR)
+ *   d_first_is_b[s] : the scaffold's first node is the contig's 'B' end (only read for single-contig scaffolds)
+ *   d_contig_len, d_re_left, d_re_right : int64 per contig id (re_counts_iteration_1)
+ * Results are bit-identical to the Python loop while the sums stay below 2^53.
+ */
+int salsa_scaffold_re(const int64_t *d_path_off, const int32_t *d_path_contig, const uint8_t *d_first_is_b,
+                      const int64_t *d_contig_len, const int64_t *d_re_left, const int64_t *d_re_right, int32_t nscaf,
+                      int64_t *d_out_left, int64_t *d_out_right, void *stream);
+
+/*
  * Hi-C physical coverage for misassembly detection.
  * Replaces break_contigs_start.cpp:307-460 (run once with -m yes,
  * run_pipeline.py:120-121) and break_contigs.cpp:199-356 (every iteration,

@@ -21,6 +21,12 @@ def engine():
     return _ENGINE
 
 
+def re_pass():
+    """The CUDA per-scaffold RE proration for salsa_b200.host.reproject.update_bed."""
+    from salsa_b200 import reproject
+    return reproject.re_pass(engine())
+
+
 def bed_pass():
     """The CUDA BED pass for salsa_b200.host.reproject.update_bed (no CPU alternative here)."""
     from salsa_b200 import reproject

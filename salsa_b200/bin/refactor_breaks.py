@@ -14,7 +14,7 @@ def main(argv=None, bed_pass=None):
     ap.add_argument('-i', '--iteration')
     ap.add_argument('-d', '--directory')
     a = ap.parse_args(argv)
-    breaks.refactor(a.directory, int(a.iteration), bed_pass or _common.bed_pass())
+    breaks.refactor(a.directory, int(a.iteration), bed_pass or _common.bed_pass(), re_pass=None if bed_pass else _common.re_pass())
     return 0
 
 

@@ -525,3 +525,62 @@ extern "C" int salsa_re_count(const uint64_t *d_planes, const uint64_t *d_blk_of
     CUDA_TRY(cudaGetLastError());
     return SALSA_OK;
 }
+
+
+// ---- per-scaffold RE counts for iterations >= 2 ---------------------------------------------------------------
+// Replaces the proration loop of layout_unitigs.py:736-814 / refactor_breaks.py:63-131: a scaffold's contigs are laid end
+// to end; RE sites of contigs left of the midpoint (Python-2 integer length/2) count left, right of it right, and the
+// contig(s) that touch the midpoint are split in proportion -- float(left+right)/len * part, summed in PATH ORDER in
+// double precision (ints and floats mix exactly as CPython's int/float additions do while sums stay below 2^53) and
+// truncated by int().  A single-contig scaffold keeps its contig's (left, right), swapped when it is reversed.
+namespace {
+__global__ void scaffold_re_kernel(const int64_t *path_off, const int32_t *path_contig, const uint8_t *first_is_b, const int64_t *clen,
+                                   const int64_t *re_left, const int64_t *re_right, int32_t nscaf, int64_t *out_left, int64_t *out_right)
+{
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nscaf) return;
+    const int64_t b = path_off[s], e = path_off[s + 1];
+    if (e - b == 1) {
+        const int32_t c = path_contig[b];
+        const int64_t l = re_left[c], r = re_right[c];
+        out_left[s] = first_is_b[s] ? l : r;
+        out_right[s] = first_is_b[s] ? r : l;
+        return;
+    }
+    int64_t total = 0;
+    for (int64_t i = b; i < e; i++) total += clen[path_contig[i]];
+    const int64_t mid = total / 2;                       // lengths are >= 0: floor == Python-2 '/'
+    double sl = 0.0, sr = 0.0;
+    int64_t off = 0;
+    for (int64_t i = b; i < e; i++) {
+        const int32_t c = path_contig[i];
+        const int64_t len = clen[c], lr = re_left[c] + re_right[c];
+        const int64_t start = off, end = off + len;
+        if (end < mid) sl = __dadd_rn(sl, (double)lr);
+        if (start > mid) sr = __dadd_rn(sr, (double)lr);
+        if (start <= mid && end >= mid) {
+            const double per = __ddiv_rn((double)lr, (double)len);
+            sl = __dadd_rn(sl, __dmul_rn(per, (double)(mid - start)));
+            sr = __dadd_rn(sr, __dmul_rn(per, (double)(end - mid)));
+        }
+        off = end;
+    }
+    out_left[s] = (int64_t)sl;                            // int(): truncation toward zero
+    out_right[s] = (int64_t)sr;
+}
+}   // namespace
+
+extern "C" int salsa_scaffold_re(const int64_t *d_path_off, const int32_t *d_path_contig, const uint8_t *d_first_is_b,
+                                 const int64_t *d_contig_len, const int64_t *d_re_left, const int64_t *d_re_right, int32_t nscaf,
+                                 int64_t *d_out_left, int64_t *d_out_right, void *stream)
+{
+    if (nscaf == 0) return SALSA_OK;
+    if (nscaf < 0 || !d_path_off || !d_path_contig || !d_first_is_b || !d_contig_len || !d_re_left || !d_re_right || !d_out_left ||
+        !d_out_right)
+        SALSA_FAIL(SALSA_ERR_ARG, "salsa_scaffold_re: bad argument");
+    scaffold_re_kernel<<<(unsigned)((nscaf + 127) / 128), 128, 0, as_stream(stream)>>>(d_path_off, d_path_contig, d_first_is_b,
+                                                                                     d_contig_len, d_re_left, d_re_right, nscaf,
+                                                                                     d_out_left, d_out_right);
+    CUDA_TRY(cudaGetLastError());
+    return SALSA_OK;
+}

@@ -74,7 +74,7 @@ def split_scaffolds(current, breakpoints, unitig_length, avoid_out):
     return new
 
 
-def refactor(directory, iteration, bed_pass):
+def refactor(directory, iteration, bed_pass, re_pass=None):
     """refactor_breaks.py -d directory -i iteration"""
     with open('%s/scaffolds_iteration_%d.p' % (directory, iteration - 1), 'rb') as f:
         current = pickle.load(f)
@@ -88,6 +88,6 @@ def refactor(directory, iteration, bed_pass):
         new = split_scaffolds(current, breakpoints, unitig_length, avoid_out)
     with open('%s/scaffolds_iteration_%d.p' % (directory, iteration - 1), 'wb') as f:
         pickle.dump(new, f)
-    reproject.update_bed(directory, new, unitig_length, iteration, refactor=True, bed_pass=bed_pass)
+    reproject.update_bed(directory, new, unitig_length, iteration, refactor=True, bed_pass=bed_pass, re_pass=re_pass)
     open('%s/misasm_%d.DONE' % (directory, iteration), 'w').close()
     return new

@@ -61,17 +61,19 @@ def scaffold_re_counts(scaffolds, info, slen, contig_length, re_counts):
     return out
 
 
-def update_bed(directory, scaffolds, contig_length, out_iteration, refactor, bed_pass):
+def update_bed(directory, scaffolds, contig_length, out_iteration, refactor, bed_pass, re_pass=None):
     """Writes alignment_iteration_{out}.bed, scaffold_length_iteration_{out}, re_counts_iteration_{out}.
     bed_pass(src, dst, c2s, info, contig_length, refactor) does the BED pass itself: the step
-    scripts pass the GPU one (salsa_b200.reproject.bed_pass)."""
+    scripts pass the GPU one (salsa_b200.reproject.bed_pass).  re_pass(scaffolds, contig_length, re_counts) ->
+    {scaffold: (left, right)} does the RE proration: the step scripts pass the GPU one
+    (salsa_b200.reproject.re_pass); without it the host loop above runs (the tests' CPU path)."""
     re_counts = {}
     with open(directory + '/re_counts_iteration_1', 'r', encoding='latin-1') as f:
         for line in f:
             a = line.split()
             re_counts[a[0]] = (int(a[1]), int(a[2]))
     c2s, info, slen = placement(scaffolds, contig_length, (lambda p: len(p) - 1) if refactor else len)
-    sre = scaffold_re_counts(scaffolds, info, slen, contig_length, re_counts)
+    sre = re_pass(scaffolds, contig_length, re_counts) if re_pass else scaffold_re_counts(scaffolds, info, slen, contig_length, re_counts)
     dst = '%s/alignment_iteration_%d.bed' % (directory, out_iteration)
     if refactor or not os.path.isfile(dst):
         bed_pass(directory + '/alignment_iteration_1.bed', dst, c2s, info, contig_length, refactor)

@@ -245,6 +245,42 @@ def _chunked_pass(eng, src, dst, refactor, tables, chunk_bytes):
     os.replace(rp + '.part', rp)
 
 
+def re_pass(eng):
+    """-> re_pass(scaffolds, contig_length, re_counts) for salsa_b200.host.reproject.update_bed: the per-scaffold RE
+    proration of layout_unitigs.py:736-814 / refactor_breaks.py:63-131 on the device (salsa_scaffold_re)."""
+    def run(scaffolds, contig_length, re_counts):
+        keys = list(scaffolds.keys())
+        cid, clen, rl, rr = {}, [], [], []
+        off, flat, first_b = [0], [], []
+        for key in keys:
+            path = scaffolds[key]
+            for i in range(0, len(path), 2):
+                contig = path[i].split(':')[0]
+                j = cid.get(contig)
+                if j is None:
+                    j = cid[contig] = len(clen)
+                    clen.append(int(contig_length[contig]))
+                    left, right = re_counts[contig]                       # KeyError like the reference's lookup
+                    rl.append(left)
+                    rr.append(right)
+                flat.append(j)
+            off.append(len(flat))
+            first_b.append(1 if path[0].split(':')[1] == 'B' else 0)
+        n = len(keys)
+        if n == 0:
+            return {}
+        dev = eng.device
+        t = lambda a, dt: torch.tensor(a, dtype=dt, device=dev)           # noqa: E731
+        d_off, d_flat, d_fb = t(off, torch.int64), t(flat, torch.int32), t(first_b, torch.uint8)
+        d_len, d_rl, d_rr = t(clen, torch.int64), t(rl, torch.int64), t(rr, torch.int64)
+        ol, orr = torch.empty(n, dtype=torch.int64, device=dev), torch.empty(n, dtype=torch.int64, device=dev)
+        check(eng.L.salsa_scaffold_re(d_off.data_ptr(), d_flat.data_ptr(), d_fb.data_ptr(), d_len.data_ptr(), d_rl.data_ptr(),
+                                      d_rr.data_ptr(), n, ol.data_ptr(), orr.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        ol, orr = ol.cpu().tolist(), orr.cpu().tolist()
+        return {k: (a, b) for k, a, b in zip(keys, ol, orr)}
+    return run
+
+
 def bed_pass(eng, background=False, chunk_bytes=None):
     """-> bed_pass(src, dst, c2s, info, contig_length, refactor) for salsa_b200.host.reproject.update_bed.
     background: return while dst is still being written (the caller promises to flush() before anything

@@ -220,3 +220,34 @@ def test_chunked_pass(eng, tmp_path, refactor, chunk):
     reproject.bed_pass(eng, chunk_bytes=chunk)(src, str(tmp_path / 'got.bed'), c2s, info, clen, refactor)
     want = open(str(tmp_path / 'want.bed'), 'rb').read()
     assert open(str(tmp_path / 'got.bed'), 'rb').read() == want and len(want) > 1000
+
+
+def test_scaffold_re_proration_matches_the_host_loop(eng):
+    """salsa_scaffold_re against the Python statement of layout_unitigs.py:736-814 (salsa_b200.host.reproject): random
+    scaffolds incl. single contigs in both orientations, contig boundaries exactly on the midpoint, zero RE counts."""
+    from salsa_b200 import reproject as gpu_reproject
+    from salsa_b200.host import reproject as host
+    rng = np.random.default_rng(11)
+    ncontig = 4000
+    names = ['ctg%05d' % i for i in range(ncontig)]
+    clen = {n: int(rng.integers(1, 3_000_000)) for n in names}
+    for k in range(0, 200, 2):                       # pairs of equal length: two-contig scaffolds split exactly at a boundary
+        clen[names[k + 1]] = clen[names[k]]
+    re_counts = {n: (int(rng.integers(0, 9000)), int(rng.integers(0, 9000))) for n in names}
+    for n in names[300:330]:
+        re_counts[n] = (0, 0)
+    scaffolds, i, sid = {}, 0, 0
+    while i < ncontig:
+        k = 2 if i < 200 else int(rng.choice([1, 1, 2, 3, 5, 8, 40]))
+        path = []
+        for n in names[i:i + k]:
+            a, b = ('B', 'E') if rng.random() < 0.5 else ('E', 'B')
+            path += [n + ':' + a, n + ':' + b]
+        scaffolds['scaffold_%d' % sid] = path
+        i += k
+        sid += 1
+    c2s, info, slen = host.placement(scaffolds, clen, len)
+    want = host.scaffold_re_counts(scaffolds, info, slen, clen, re_counts)
+    got = gpu_reproject.re_pass(eng)(scaffolds, clen, re_counts)
+    assert got == want
+    assert list(got.keys()) == list(want.keys())            # file order = dict order
