@@ -357,6 +357,22 @@ int salsa_re_count(const uint64_t *d_planes, const uint64_t *d_blk_off, const ui
                    uint64_t *d_occ_scratch, void *stream);
 
 /*
+ * BED rewrite of the cleaning step (-m yes).  Replaces the streaming loop of correct.py:62-92: a line on a contig that
+ * was not cut is copied as its first four fields; a line on a cut contig is dropped when it straddles the cut, keeps
+ * its coordinates as `contig_1` left of it, and becomes `contig_2` with both coordinates shifted otherwise.
+ *   d_cut[id]       : cut position of the contig (salsa_names_build ids), -1 = not cut
+ *   d_line_start[i] : byte offset of line i in d_bed (every line, in file order)
+ * salsa_clean_bed_plan writes what each line will emit (bytes; 0 = dropped) and the first error as
+ * (offset << 8 | code) in *d_err (UINT64_MAX when clean; 1 IndexError, 2 ValueError, 3 KeyError -- where the reference
+ * would die).  The caller turns the lengths into offsets -- and zeroes the lengths of the lines the reference loses:
+ * its last, partial buffer of 1,000,000 lines is never written (correct.py:87-92) -- and salsa_clean_bed_emit writes.
+ */
+int salsa_clean_bed_plan(salsa_ctx *ctx, const void *d_bed, size_t nbytes, const int64_t *d_cut, const int64_t *d_line_start,
+                         size_t nlines, uint32_t *d_out_len, uint64_t *d_err, void *stream);
+int salsa_clean_bed_emit(salsa_ctx *ctx, const void *d_bed, size_t nbytes, const int64_t *d_cut, const int64_t *d_line_start,
+                         size_t nlines, const uint32_t *d_out_len, const int64_t *d_out_off, void *d_out, void *stream);
+
+/*
  * RE counts of the scaffolds of iterations >= 2.  Replaces layout_unitigs.py:736-814 and refactor_breaks.py:63-131:
  * the contigs of a scaffold lie end to end; contigs wholly left / right of the midpoint (integer length/2) give all
  * their sites to that side, the contig(s) touching the midpoint are split in proportion

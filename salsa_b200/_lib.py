@@ -63,6 +63,8 @@ SIGNATURES = {
     'salsa_sparse_segment_bytes': (c_size_t, [c_size_t]),
     'salsa_sparse_partition': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_size_t, c_void_p, c_void_p, c_void_p]),
     'salsa_sparse_add_segments': (C.c_int, [c_void_p, c_i32, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p]),
+    'salsa_clean_bed_plan': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
+    'salsa_clean_bed_emit': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_void_p]),
     'salsa_scaffold_re': (C.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p]),
     'salsa_g12': (C.c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_void_p]),
     'salsa_links_score': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32] + [c_void_p] * 10),

@@ -21,6 +21,12 @@ def engine():
     return _ENGINE
 
 
+def clean_pass():
+    """The CUDA BED rewrite for salsa_b200.host.clean.clean."""
+    from salsa_b200 import reproject
+    return reproject.clean_pass(engine())
+
+
 def re_pass():
     """The CUDA per-scaffold RE proration for salsa_b200.host.reproject.update_bed."""
     from salsa_b200 import reproject

@@ -256,3 +256,149 @@ def exchange_segments(tkeys, tcounts, ops, slot_cap, group=None):
     else:
         recv = send
     return ops.add(recv, world, slot_cap)
+
+
+# ---------------------------------------------------------------- RE-site counting, sharded by contig
+def fasta_shard_ranges(view, world):
+    """Cut a FASTA (anything indexable as bytes) into `world` byte ranges that each start on a record header ('>' at a
+    line start) and are balanced by bytes, i.e. by bases: records are independent units (RE_sites.py:30-88 counts per
+    contig), so a rank runs the whole single-GPU path on its range.  Returns [(lo, hi)] * world; empty shards are (hi, hi)."""
+    n = len(view)
+    if n == 0:
+        return [(0, 0)] * world
+
+    def header_at_or_after(p):
+        if p <= 0:
+            return 0
+        step = 1 << 22
+        q = p - 1                                         # a header starts right after a newline
+        while q < n:
+            blk = np.frombuffer(bytes(view[q:min(n, q + step)]), dtype=np.uint8)
+            hit = np.flatnonzero((blk[:-1] == 10) & (blk[1:] == 62))
+            if len(hit):
+                return q + int(hit[0]) + 1
+            q += step - 1                                 # overlap one byte: a "\n>" may straddle the blocks
+        return n
+
+    cuts = [0]
+    for k in range(1, world):
+        cuts.append(max(cuts[-1], header_at_or_after(n * k // world)))
+    cuts.append(n)
+    return [(cuts[k], cuts[k + 1]) if cuts[k + 1] > cuts[k] else (cuts[k + 1], cuts[k + 1]) for k in range(world)]
+
+
+def merge_site_counts(parts):
+    """parts: per rank (names, left, right, seqlen) in rank order = file order.  The reference fills dicts keyed by
+    record name (RE_sites.py:19,61): a repeated name keeps its first position and its last sequence."""
+    order, last = [], {}
+    for names, left, right, seqlen in parts:
+        for i, nm in enumerate(names):
+            if nm not in last:
+                order.append(nm)
+            last[nm] = (int(left[i]), int(right[i]), int(seqlen[i]))
+    left = np.array([last[nm][0] for nm in order], dtype=np.int64)
+    right = np.array([last[nm][1] for nm in order], dtype=np.int64)
+    seqlen = np.array([last[nm][2] for nm in order], dtype=np.int64)
+    return order, left, right, seqlen
+
+
+def count_sites_sharded(count_fn, fasta, enzyme, group=None):
+    """RE-site counting over all ranks of the process group: rank r counts the records of its byte range with
+    count_fn(shard, enzyme) -> (names, left, right, seqlen) (salsa_b200.re_sites.count_sites bound to an Engine; the CPU
+    tests pass the oracle's), the per-contig results -- two integers per contig -- are all-gathered, and every rank
+    returns the whole table.  An error on any rank (a ':' in a header, a bad enzyme) is raised on every rank."""
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    lo, hi = fasta_shard_ranges(fasta, world)[rank]
+    mine, err = ([], [], [], []), None
+    try:
+        if hi > lo:
+            names, left, right, seqlen = count_fn(fasta[lo:hi], enzyme)
+            mine = (list(names), [int(x) for x in left], [int(x) for x in right], [int(x) for x in seqlen])
+        elif rank == 0:
+            mine = tuple(list(x) for x in count_fn(fasta[0:0], enzyme))
+    except Exception as e:           # noqa: BLE001  (re-raised below, on every rank)
+        err = e
+    if world > 1:
+        parts = [None] * world
+        dist.all_gather_object(parts, (mine, None if err is None else (type(err).__name__, str(err))), group=group)
+    else:
+        parts = [(mine, None if err is None else (type(err).__name__, str(err)))]
+    for r, (_, e) in enumerate(parts):
+        if e is not None:
+            if err is not None:
+                raise err
+            raise RuntimeError('rank %d: %s: %s' % (r, e[0], e[1]))
+    return merge_site_counts([p for p, _ in parts])
+
+
+# ---------------------------------------------------------------- coverage (misassembly detection), sharded by contig
+def shard_lengths(lengths_text, world, min_len=1_000_000):
+    """Deal the lines of a lengths file (`name\tlen...`) to `world` ranks: contigs of at least `min_len` bases -- the only
+    ones the coverage programs look at (break_contigs_start.cpp:325, break_contigs.cpp:218-225) -- longest first to the
+    least loaded rank; shorter ones all to rank 0 (they cost nothing).  Every rank's text keeps the file's line order.
+    Returns a list of `world` texts (bytes)."""
+    lines = [ln for ln in lengths_text.split(b'\n') if ln.strip()]
+    big = []
+    for i, ln in enumerate(lines):
+        a = ln.split()
+        try:
+            v = int(float(a[1]))
+        except (IndexError, ValueError):
+            v = 0
+        big.append((v, i))
+    load, owner = [0] * world, [0] * len(lines)
+    for v, i in sorted(big, key=lambda t: (-t[0], t[1])):
+        if v >= min_len:
+            r = min(range(world), key=lambda k: (load[k], k))
+            owner[i] = r
+            load[r] += v
+    return [b''.join(lines[i] + b'\n' for i in range(len(lines)) if owner[i] == r) for r in range(world)]
+
+
+def merge_coverage_reports(parts, joins):
+    """Per-rank stdout of break_contigs_start (joins = False: `contig\tposition` lines) or break_contigs (joins = True:
+    `scaffold(\tpos)*` lines + the three summary lines of break_contigs.cpp:353-355) -> one report.  The per-contig lines
+    are independent; the summary counts add up and the percentage is recomputed as the reference prints it
+    (cout << double: 6 significant digits; 0/0 prints -nan)."""
+    body, total, susp = [], 0, 0
+    for text in parts:
+        for ln in text.split(b'\n'):
+            if not ln:
+                continue
+            if joins and ln.startswith(b'Total Joins = '):
+                total += int(ln.split(b'=')[1])
+            elif joins and ln.startswith(b'Suspicious Joins = '):
+                susp += int(ln.split(b'=')[1])
+            elif joins and ln.startswith(b'Percent Suspicious Joins = '):
+                pass
+            else:
+                body.append(ln)
+    out = b''.join(ln + b'\n' for ln in body)
+    if joins:
+        pct = b'-nan' if total == 0 else ('%g' % (susp * 100.0 / total)).encode()
+        out += b'Total Joins = %d\nSuspicious Joins = %d\nPercent Suspicious Joins = %s\n' % (total, susp, pct)
+    return out
+
+
+def coverage_sharded(run_fn, lengths_path, joins, workdir, group=None):
+    """The coverage programs over all ranks: contigs are independent units (one difference array each), so rank r runs
+    the whole program -- run_fn(lengths_path_r) -> stdout bytes -- on ITS contigs only (its lines of the lengths file;
+    every other contig then counts as unknown, which the programs skip exactly like a short one) and the reports are
+    gathered and merged.  Every rank scans the whole BED (it is resident on every GPU anyway; the scan is 12 of 90 ms at
+    BASELINE size), the prefix/Kadane analysis -- the bulk -- is split.  Returns the merged report on every rank."""
+    import os
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    with open(lengths_path, 'rb') as f:
+        texts = shard_lengths(f.read(), world)
+    mine = os.path.join(workdir, 'lengths.rank%d' % rank)
+    with open(mine, 'wb') as f:
+        f.write(texts[rank])
+    text = run_fn(mine)
+    if world > 1:
+        parts = [None] * world
+        dist.all_gather_object(parts, text, group=group)
+    else:
+        parts = [text]
+    return merge_coverage_reports(parts, joins)

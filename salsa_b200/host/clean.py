@@ -59,7 +59,9 @@ def wrap_fasta(s, width=80):
     return out.tobytes() + (tail + b'\n' if tail else b'')
 
 
-def clean(assembly, breaks_path, bed, outdir, flush_every=1000000):
+def clean(assembly, breaks_path, bed, outdir, flush_every=1000000, bed_pass=None):
+    """bed_pass(src, dst, names, cut, flush_every) does the BED rewrite: the step script passes the CUDA one
+    (salsa_b200.reproject.clean_pass); without it the line loop below runs (the tests' CPU path)."""
     seqs = read_fasta(assembly)
     cut = {}
     with open(breaks_path, 'r', encoding='latin-1') as f:
@@ -73,17 +75,34 @@ def clean(assembly, breaks_path, bed, outdir, flush_every=1000000):
             new_seq[name + '_2'] = s[cut[name]:]
         else:
             new_seq[name] = s
-    with open(outdir + '/alignment_iteration_1.tmp.bed', 'w', encoding='latin-1', newline='\n') as out, \
-            open(bed, 'r', encoding='latin-1', newline='\n') as f:
+    if bed_pass is not None:
+        bed_pass(bed, outdir + '/alignment_iteration_1.tmp.bed', list(seqs.keys()), cut, flush_every)
+    else:
+        _clean_bed_lines(bed, outdir + '/alignment_iteration_1.tmp.bed', seqs, cut, flush_every)
+    with open(outdir + '/asm.cleaned.fasta', 'wb') as fo:
+        for name, s in new_seq.items():
+            fo.write(('>' + name + '\n').encode('latin-1'))
+            fo.write(wrap_fasta(s))
+    with open(outdir + '/scaffold_length_iteration_1', 'w') as fo:
+        for name, s in new_seq.items():
+            fo.write('%s\t%d\n' % (name, len(s)))
+
+
+def _clean_bed_lines(bed, dst, seqs, cut, flush_every):
+    with open(dst, 'w', encoding='latin-1', newline='\n') as out, open(bed, 'r', encoding='latin-1', newline='\n') as f:
         buf = []
         for line in f:
             a = line.split()
             if a[0] not in cut:
+                if a[0] not in seqs:
+                    raise KeyError(a[0])                       # contig2new[attrs[0]], correct.py:69
                 buf.append('%s\t%s\t%s\t%s\n' % (a[0], a[1], a[2], a[3]))
             else:
                 p1, p2, bp = int(a[1]), int(a[2]), cut[a[0]]
                 if p1 < bp and p2 > bp:
                     continue                                   # straddles the break: dropped
+                if a[0] not in seqs:
+                    raise KeyError(a[0])                       # contig2new[attrs[0]][k], correct.py:81,86
                 if p2 < bp:
                     buf.append('%s_1\t%s\t%s\t%s\n' % (a[0], a[1], a[2], a[3]))
                 else:
@@ -92,10 +111,3 @@ def clean(assembly, breaks_path, bed, outdir, flush_every=1000000):
                 out.writelines(buf)
                 buf = []
         # (no final flush: see module docstring)
-    with open(outdir + '/asm.cleaned.fasta', 'wb') as fo:
-        for name, s in new_seq.items():
-            fo.write(('>' + name + '\n').encode('latin-1'))
-            fo.write(wrap_fasta(s))
-    with open(outdir + '/scaffold_length_iteration_1', 'w') as fo:
-        for name, s in new_seq.items():
-            fo.write('%s\t%d\n' % (name, len(s)))

@@ -245,6 +245,69 @@ def _chunked_pass(eng, src, dst, refactor, tables, chunk_bytes):
     os.replace(rp + '.part', rp)
 
 
+def clean_pass(eng):
+    """-> bed_pass(src, dst, names, cut, flush_every) for salsa_b200.host.clean.clean: the BED rewrite of correct.py:62-92
+    on the device (salsa_clean_bed_plan / salsa_clean_bed_emit).  Line starts and the prefix sums between the two
+    kernels are torch ops; the reference's lost tail (its last, partial buffer of `flush_every` lines is never written)
+    is applied to the ranks of the kept lines.  The cleaned BED stays resident for the steps that follow."""
+    from ._lib import DataError
+
+    def run(src, dst, names, cut, flush_every):
+        dev = eng.device
+        bed = resident_bed(src, dev, load=True)
+        nb = [n.encode('latin-1') for n in names]
+        eng.set_contigs(nb, np.zeros(len(nb), np.int64))
+        idx = {n: i for i, n in enumerate(eng.names)}
+        cut_arr = np.full(max(len(eng.names), 1), -1, np.int64)
+        for k, v in cut.items():
+            j = idx.get(k.encode('latin-1'))
+            if j is not None:
+                if v < 0:
+                    raise ValueError('negative break position for %r' % k)
+                cut_arr[j] = v
+        d_cut = torch.from_numpy(cut_arr).to(dev)
+        n = bed.numel()
+        st = torch.cuda.current_stream().cuda_stream
+        starts = torch.nonzero(bed == 10).flatten() + 1
+        starts = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), starts]) if n else starts
+        if starts.numel() and int(starts[-1]) >= n:
+            starts = starts[:-1]                                   # the file ends with a newline: no line starts there
+        nl = starts.numel()
+        out_len = torch.empty(max(nl, 1), dtype=torch.int32, device=dev)
+        err = torch.empty(1, dtype=torch.int64, device=dev)
+        check(eng.L.salsa_clean_bed_plan(eng.ctx, bed.data_ptr(), n, d_cut.data_ptr(), starts.data_ptr(), nl, out_len.data_ptr(),
+                                         err.data_ptr(), st))
+        e = int(err.item())
+        if e != -1:
+            raise DataError(e & 0xff, (e >> 8) & ((1 << 56) - 1))
+        out_len = out_len[:nl]
+        keep = out_len > 0
+        rank = torch.cumsum(keep, 0)                               # 1-based rank among the kept lines
+        kept = int(rank[-1]) if nl else 0
+        limit = kept // flush_every * flush_every                  # correct.py:87-92: the last partial buffer is lost
+        out_len = torch.where(keep & (rank <= limit), out_len, torch.zeros_like(out_len))
+        off = torch.cumsum(out_len.to(torch.int64), 0) - out_len
+        total = int((off[-1] + out_len[-1]).item()) if nl else 0
+        out = torch.empty(total, dtype=torch.uint8, device=dev)
+        if nl and total:
+            check(eng.L.salsa_clean_bed_emit(eng.ctx, bed.data_ptr(), n, d_cut.data_ptr(), starts.data_ptr(), nl, out_len.data_ptr(),
+                                             off.data_ptr(), out.data_ptr(), st))
+        torch.cuda.current_stream().synchronize()
+        with open(dst, 'wb') as f:
+            pos = 0
+            while pos < total:
+                k = min(CHUNK, total - pos)
+                out[pos:pos + k].cpu().numpy().tofile(f)
+                pos += k
+        st_ = os.stat(dst)
+        _remember(os.path.realpath(dst), st_.st_size, st_.st_mtime_ns, out)
+        # run_pipeline.py:125 moves the file to alignment_iteration_1.bed (same size, same mtime): known under that name too
+        final = os.path.join(os.path.dirname(os.path.realpath(dst)), 'alignment_iteration_1.bed')
+        if final != os.path.realpath(dst):
+            _remember(final, st_.st_size, st_.st_mtime_ns, out)
+    return run
+
+
 def re_pass(eng):
     """-> re_pass(scaffolds, contig_length, re_counts) for salsa_b200.host.reproject.update_bed: the per-scaffold RE
     proration of layout_unitigs.py:736-814 / refactor_breaks.py:63-131 on the device (salsa_scaffold_re)."""

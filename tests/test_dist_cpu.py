@@ -55,6 +55,74 @@ def test_shard_ranges_cover_every_pair_once(oracle_lib):
     assert sum(hi - lo for lo, hi in shard_ranges(one_line, 4)) >= len(one_line)
 
 
+def test_fasta_shards_and_merge(oracle_lib):
+    """RE counting shards by contig: byte ranges cut at record headers, each counted on its own (here by the oracle),
+    merged with the reference's dict semantics -- equal to counting the whole file, for any number of ranks."""
+    from salsa_b200 import synth
+    from salsa_b200.dist import fasta_shard_ranges, merge_site_counts
+    asm = synth.make_assembly(ncontig=23, genome=400_000, len_lo=2_000, len_hi=60_000, nchrom=3, seed=5)
+    fa = synth.gen_fasta(asm)
+    fa += b'>' + asm.names[3] + b' again\nGATCGATCNNGANTCGAGTC\n'       # a repeated name: first position, last sequence
+    whole = oracle_lib.re_sites(fa, 'GATC,GANTC')
+    for world in (1, 2, 3, 7, 64):
+        ranges = fasta_shard_ranges(fa, world)
+        assert len(ranges) == world and ranges[0][0] == 0 and ranges[-1][1] == len(fa)
+        parts = []
+        for lo, hi in ranges:
+            assert hi == lo or fa[lo:lo + 1] == b'>'
+            parts.append(oracle_lib.re_sites(fa[lo:hi], 'GATC,GANTC') if hi > lo else ([], [], [], []))
+        names, left, right, seqlen = merge_site_counts(parts)
+        assert names == list(whole[0]) and (left == whole[1]).all() and (right == whole[2]).all() and (seqlen == whole[3]).all()
+    assert fasta_shard_ranges(b'', 3) == [(0, 0)] * 3
+
+
+def test_coverage_sharded_by_contig_equals_one_run(tmp_path):
+    """Coverage shards by contig: the lengths file is dealt to the ranks, each runs the whole program on its contigs
+    (here the compiled reference programs), the merged report equals the one-process report."""
+    import subprocess
+    import cases
+    import oracle
+    from salsa_b200.dist import merge_coverage_reports, shard_lengths
+    if not oracle.ref_binary('break_contigs_start'):
+        import pytest
+        pytest.skip('oracle/_ref not built')
+    d = str(tmp_path)
+    seed, lens, holes, npairs = cases.COV_START_CASES['two_contigs']
+    names, L, bed = cases.coverage_case(seed, lens, holes, npairs)
+    open(d + '/b.bed', 'wb').write(bed)
+    ltxt = cases.lengths_text(names, L)
+    open(d + '/l.txt', 'wb').write(ltxt)
+    run = lambda lp: subprocess.run([oracle.ref_binary('break_contigs_start'), '-a', d + '/b.bed', '-l', lp, '-s', '100'],       # noqa: E731
+                                    capture_output=True, check=True).stdout
+    whole = run(d + '/l.txt')
+    assert whole.strip()
+    for world in (2, 3):
+        texts = shard_lengths(ltxt, world)
+        assert sorted(b''.join(texts).split(b'\n')) == sorted(ltxt.split(b'\n'))
+        parts = []
+        for r, t in enumerate(texts):
+            open(d + '/l%d.txt' % r, 'wb').write(t)
+            parts.append(run(d + '/l%d.txt' % r))
+        assert sorted(merge_coverage_reports(parts, False).split(b'\n')) == sorted(whole.split(b'\n'))
+    # the joins variant: summary lines add up
+    seed, lens, holes, npairs, bp = cases.COV_JOIN_CASES['join_ok_and_bad']
+    names, L, bed = cases.coverage_case(seed, lens, holes, npairs, scaffold_style=True)
+    open(d + '/b.bed', 'wb').write(bed)
+    ltxt = cases.lengths_text(names, L)
+    open(d + '/l.txt', 'wb').write(ltxt)
+    open(d + '/bp.txt', 'wb').write(cases.breakpoints_text({names[k]: v for k, v in bp.items()}))
+    runj = lambda lp: subprocess.run([oracle.ref_binary('break_contigs'), '-a', d + '/b.bed', '-l', lp, '-b', d + '/bp.txt', '-i', '2',     # noqa: E731
+                                      '-s', '100'], capture_output=True, check=True).stdout
+    whole = runj(d + '/l.txt')
+    parts = []
+    for r, t in enumerate(shard_lengths(ltxt, 2)):
+        open(d + '/l%d.txt' % r, 'wb').write(t)
+        parts.append(runj(d + '/l%d.txt' % r))
+    merged = merge_coverage_reports(parts, True)
+    keep = lambda t: sorted(ln for ln in t.split(b'\n') if ln.strip() and len(ln.split()) >= 2)          # noqa: E731
+    assert keep(merged) == keep(whole)
+
+
 WORKER = r'''
 import os, sys
 sys.path.insert(0, %r)
@@ -99,6 +167,20 @@ for ks, cs in zip(g2k, g2c):
         assert k not in got2
         got2[k] = c
 assert got2 == want
+# RE counting sharded by contig: every rank counts its records (here with the oracle), all ranks end with the whole table
+import oracle
+from salsa_b200 import synth
+from salsa_b200.dist import count_sites_sharded
+asm = synth.make_assembly(ncontig=17, genome=300_000, len_lo=2_000, len_hi=50_000, nchrom=3, seed=6)
+fa = synth.gen_fasta(asm)
+got_re = count_sites_sharded(lambda shard, enz: oracle.re_sites(bytes(shard), enz), fa, 'GATC,GANTC')
+want_re = oracle.re_sites(fa, 'GATC,GANTC')
+assert got_re[0] == list(want_re[0]) and (got_re[1] == want_re[1]).all() and (got_re[2] == want_re[2]).all()
+try:
+    count_sites_sharded(lambda shard, enz: oracle.re_sites(bytes(shard), enz), fa, 'EcoRI')      # a bad enzyme: raised on every rank
+    raise SystemExit('no error')
+except (RuntimeError, oracle.OracleError):
+    pass
 # dense merge: all-reduce(sum)
 t = torch.full((64,), r + 1, dtype=torch.int64)
 merge_dense(t)

@@ -103,9 +103,72 @@ def test_segment_partition_and_add_kernels():
     eng.close()
 
 
+def test_re_counting_sharded_by_contig_equals_whole_file():
+    """The multi-GPU RE path with its ranks emulated on one GPU: every shard of the FASTA (cut at record headers) goes
+    through the single-GPU kernels on its own, the merged table must equal the whole-file run and the oracle."""
+    import oracle
+    from salsa_b200 import synth
+    from salsa_b200.dist import fasta_shard_ranges, merge_site_counts
+    from salsa_b200.engine import Engine
+    from salsa_b200.re_sites import count_sites
+    eng = Engine(0)
+    asm = synth.make_assembly(ncontig=31, genome=900_000, len_lo=2_000, len_hi=90_000, nchrom=3, seed=8)
+    fa = synth.gen_fasta(asm)
+    buf = np.frombuffer(fa, dtype=np.uint8)
+    for enz in ('GATC,GANTC', 'AAGCTT', 'DNASE'):
+        whole = count_sites(eng, buf, enz)
+        for world in (2, 5):
+            parts = [count_sites(eng, buf[lo:hi], enz) if hi > lo else ([], [], [], []) for lo, hi in fasta_shard_ranges(fa, world)]
+            names, left, right, seqlen = merge_site_counts(parts)
+            assert names == list(whole[0]) and (left == whole[1]).all() and (right == whole[2]).all() and (seqlen == whole[3]).all()
+        if enz != 'DNASE':
+            o = oracle.re_sites(fa, enz)
+            assert list(o[0]) == list(whole[0]) and (o[1] == whole[1]).all() and (o[2] == whole[2]).all()
+    eng.close()
+
+
+def test_coverage_sharded_by_contig_equals_one_run(tmp_path):
+    """The multi-GPU coverage path with its ranks emulated on one GPU: the drop-in break_contigs_start / break_contigs run on
+    every rank's share of the lengths file; the merged report equals the one-process report."""
+    import subprocess
+    import cases
+    from salsa_b200.dist import merge_coverage_reports, shard_lengths
+    binp = os.path.join(ROOT, 'salsa_b200', 'bin')
+    d = str(tmp_path)
+    seed, lens, holes, npairs = cases.COV_START_CASES['two_contigs']
+    names, L, bed = cases.coverage_case(seed, lens, holes, npairs)
+    open(d + '/b.bed', 'wb').write(bed)
+    ltxt = cases.lengths_text(names, L)
+    open(d + '/l.txt', 'wb').write(ltxt)
+    run = lambda lp: subprocess.run([binp + '/break_contigs_start', '-a', d + '/b.bed', '-l', lp, '-s', '100'],       # noqa: E731
+                                    capture_output=True, check=True).stdout
+    whole = run(d + '/l.txt')
+    assert whole.strip()
+    parts = []
+    for r, t in enumerate(shard_lengths(ltxt, 2)):
+        open(d + '/l%d.txt' % r, 'wb').write(t)
+        parts.append(run(d + '/l%d.txt' % r))
+    assert sorted(merge_coverage_reports(parts, False).split(b'\n')) == sorted(whole.split(b'\n'))
+    seed, lens, holes, npairs, bp = cases.COV_JOIN_CASES['join_ok_and_bad']
+    names, L, bed = cases.coverage_case(seed, lens, holes, npairs, scaffold_style=True)
+    open(d + '/b.bed', 'wb').write(bed)
+    ltxt = cases.lengths_text(names, L)
+    open(d + '/l.txt', 'wb').write(ltxt)
+    open(d + '/bp.txt', 'wb').write(cases.breakpoints_text({names[k]: v for k, v in bp.items()}))
+    runj = lambda lp: subprocess.run([binp + '/break_contigs', '-a', d + '/b.bed', '-l', lp, '-b', d + '/bp.txt', '-i', '2', '-s', '100'],       # noqa: E731
+                                     capture_output=True, check=True).stdout
+    whole = runj(d + '/l.txt')
+    parts = []
+    for r, t in enumerate(shard_lengths(ltxt, 2)):
+        open(d + '/l%d.txt' % r, 'wb').write(t)
+        parts.append(runj(d + '/l%d.txt' % r))
+    assert sorted(merge_coverage_reports(parts, True).split(b'\n')) == sorted(whole.split(b'\n'))
+
+
 WORKER = r'''
 import os, sys
 sys.path.insert(0, %r)
+sys.path.insert(0, os.path.join(sys.path[0], 'tests'))
 import numpy as np, torch, torch.distributed as dist
 import oracle
 from salsa_b200 import synth
@@ -160,6 +223,33 @@ for p in parts:
         assert kk not in merged
         merged[kk] = vv
 assert merged == want
+# RE counting sharded by contig over the ranks
+from salsa_b200.dist import count_sites_sharded
+from salsa_b200.re_sites import count_sites
+fa = synth.gen_fasta(asm)
+fbuf = np.frombuffer(fa, dtype=np.uint8)
+got_re = count_sites_sharded(lambda shard, enz: count_sites(eng, shard, enz), fbuf, 'GATC,GANTC')
+want_re = oracle.re_sites(fa, 'GATC,GANTC')
+assert got_re[0] == list(want_re[0]) and (got_re[1] == want_re[1]).all() and (got_re[2] == want_re[2]).all()
+# coverage sharded by contig over the ranks (the library call the drop-in programs wrap)
+import ctypes, tempfile, cases
+from salsa_b200.dist import coverage_sharded
+from salsa_b200 import _lib
+wd = tempfile.mkdtemp()
+cseed, clens, choles, cpairs = cases.COV_START_CASES['two_contigs']
+cnames, cL, cbed = cases.coverage_case(cseed, clens, choles, cpairs)
+open(wd + '/b.bed', 'wb').write(cbed)
+open(wd + '/l.txt', 'wb').write(cases.lengths_text(cnames, cL))
+def run_cov(lp):
+    argv = ['-a', wd + '/b.bed', '-l', lp, '-s', '100']
+    arr = (ctypes.c_char_p * len(argv))(*[a.encode() for a in argv])
+    outp = wd + '/out.rank%%d' %% rank
+    assert _lib.lib().salsa_break_contigs_run(0, len(argv), arr, None, 0, outp.encode()) == 0
+    return open(outp, 'rb').read()
+rep = coverage_sharded(run_cov, wd + '/l.txt', False, wd)
+import json
+want_cov = json.load(open(os.path.join(%r, 'tests', 'golden', 'coverage_ref.json')))['start']['two_contigs']
+assert sorted(rep.decode().split('\n'))[1:] == sorted(want_cov) or sorted(x for x in rep.decode().split('\n') if x) == sorted(want_cov)
 dist.barrier()
 dist.destroy_process_group()
 sys.stdout.write('rank %%d ok\n' %% rank)     # one write per rank: no interleaving
@@ -169,7 +259,7 @@ sys.stdout.write('rank %%d ok\n' %% rank)     # one write per rank: no interleav
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs')
 def test_two_rank_nccl_sharded_ingest_and_merge(tmp_path):
     script = tmp_path / 'worker.py'
-    script.write_text(WORKER % ROOT)
+    script.write_text(WORKER % (ROOT, ROOT))
     r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr',
                         '127.0.0.1', '--master-port', '29551', str(script)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

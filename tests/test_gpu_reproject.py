@@ -251,3 +251,50 @@ def test_scaffold_re_proration_matches_the_host_loop(eng):
     got = gpu_reproject.re_pass(eng)(scaffolds, clen, re_counts)
     assert got == want
     assert list(got.keys()) == list(want.keys())            # file order = dict order
+
+
+def test_clean_bed_pass_matches_the_host_loop(eng, tmp_path):
+    """salsa_clean_bed_plan / _emit (correct.py:62-92 on the device) against the line loop of salsa_b200.host.clean:
+    cut and uncut contigs, lines left of / right of / across the cut, every str.split() separator, extra columns,
+    the lost tail at several buffer sizes, and the errors the reference would die with."""
+    from salsa_b200 import reproject as gpu_reproject
+    from salsa_b200.engine import DataError
+    from salsa_b200.host import clean
+    rng = np.random.default_rng(3)
+    names = ['c%d' % i for i in range(40)] + ['a_rather_long_contig_name_%d' % i for i in range(5)]
+    seqs = {n: 'A' * 10 for n in names}
+    cut = {n: int(rng.integers(100, 5000)) for n in names[::3]}
+    seps = ['\t', ' ', '  ', '\t ', '\x0b', '\r']
+    lines = []
+    for i in range(5000):
+        c = names[int(rng.integers(len(names)))]
+        s0 = int(rng.integers(0, 6000))
+        e0 = s0 + int(rng.integers(1, 400))
+        if c in cut and rng.random() < 0.2:
+            s0, e0 = cut[c] - int(rng.integers(0, 3)), cut[c] + int(rng.integers(0, 3))      # around the cut, equality included
+        sep = lambda: seps[int(rng.integers(len(seps)))]                                     # noqa: E731
+        tail = ['', '\t60\t+', ' x y z'][int(rng.integers(3))]
+        lines.append(c + sep() + ('+' if rng.random() < 0.02 else '') + str(s0) + sep() + str(e0) + sep() + 'r%d/%d' % (i // 2, 1 + i % 2) + tail)
+    text = '\n'.join(lines) + '\n'
+    src = str(tmp_path / 'in.bed')
+    open(src, 'w', newline='\n').write(text)
+    for flush in (1000000, 1000, 7, 1):
+        want, got = str(tmp_path / 'want.bed'), str(tmp_path / 'got.bed')
+        clean._clean_bed_lines(src, want, seqs, cut, flush)
+        gpu_reproject.clean_pass(eng)(src, got, names, cut, flush)
+        assert open(got, 'rb').read() == open(want, 'rb').read(), flush
+    assert os.path.getsize(str(tmp_path / 'got.bed')) > 1000                                  # flush = 1 keeps everything
+    # no trailing newline, and the errors
+    for bad, code in (('c1 5 9 r/1\nc1 5 9', 1), ('c1 5 9 r/1\n\nc1 5 9 r/2\n', 1), ('zz 5 9 r/1\n', 3), ('c0 5x 9 r/1\n', 2),
+                      ('c1 5x 9 r/1\n', None)):
+        open(src, 'w', newline='\n').write(bad)
+        if code is None:                          # c1 is not cut: its coordinates are copied as text, never parsed
+            assert 'c1' not in cut
+            gpu_reproject.clean_pass(eng)(src, str(tmp_path / 'g2.bed'), names, cut, 1)
+            assert open(str(tmp_path / 'g2.bed')).read() == 'c1\t5x\t9\tr/1\n'
+            continue
+        with pytest.raises(DataError) as ge:
+            gpu_reproject.clean_pass(eng)(src, str(tmp_path / 'g2.bed'), names, cut, 1)
+        assert ge.value.code == code
+        with pytest.raises((IndexError, KeyError, ValueError)):
+            clean._clean_bed_lines(src, str(tmp_path / 'w2.bed'), seqs, cut, 1)
