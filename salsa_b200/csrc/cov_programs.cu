@@ -188,7 +188,11 @@ static int run(bool joins, map<string, string> &opt, const char *d_resident, siz
         while (begin < fsz && bed[begin] == '\n') begin++;
     }
 
-    int device = getenv("SALSA_B200_DEVICE") ? atoi(getenv("SALSA_B200_DEVICE")) : 0;
+    // SALSA_B200_DEVICE if set, else the caller's current device (one process per GPU: a rank of a multi-GPU run calls this
+    // with its own device current; a stand-alone program starts on device 0)
+    int device = -1;
+    if (getenv("SALSA_B200_DEVICE")) device = atoi(getenv("SALSA_B200_DEVICE"));
+    else if (cudaGetDevice(&device) != cudaSuccess) device = 0;
     salsa_ctx *ctx = NULL;
     CK(salsa_ctx_create(device, &ctx));
     uint8_t *h_touched = (uint8_t *)calloc((size_t)n + 1, 1);
