@@ -29,16 +29,60 @@ constexpr int FTHREADS = 256;
 
 __device__ __forceinline__ bool is_ws_b(uint32_t c) { return c == 32u || (c - 9u) <= 4u; }
 
+// ---- exact SWAR byte tests (0x80 in every byte that satisfies the test) and 16-flag packing ----
+__device__ __forceinline__ uint32_t eq4(uint32_t w, uint32_t c4)
+{
+    uint32_t x = w ^ c4;
+    uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
+    return ~(t | x) & 0x80808080u;
+}
+__device__ __forceinline__ uint32_t le20_4(uint32_t w)
+{
+    uint32_t t = (w & 0x7F7F7F7Fu) + 0x5F5F5F5Fu;
+    return ~(t | w) & 0x80808080u;
+}
+__device__ __forceinline__ uint32_t pack16f(uint32_t z0, uint32_t z1, uint32_t z2, uint32_t z3)
+{
+    uint32_t lo = __dp4a(z0, 0x08040201u, 0u);
+    lo = __dp4a(z1, 0x80402010u, lo);
+    uint32_t hi = __dp4a(z2, 0x08040201u, 0u);
+    hi = __dp4a(z3, 0x80402010u, hi);
+    return (lo >> 7) | (hi << 1);
+}
+
 // ---- 1. header positions ------------------------------------------------
+// 16 bytes per thread and load; a '>' is a header only at the start of the text or right after a newline
 __global__ void fasta_headers_kernel(const uint8_t *txt, size_t n, unsigned long long *out, unsigned int *count,
                                      unsigned int cap)
 {
+    const size_t n16 = n / 16;
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) {
-        if (txt[i] == '>' && (i == 0 || txt[i - 1] == '\n')) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const bool aligned = ((uintptr_t)txt & 15u) == 0;
+    for (; i < n16; i += stride) {
+        uint32_t m;
+        if (aligned) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(txt) + i);
+            m = pack16f(eq4(v.x, 0x3E3E3E3Eu), eq4(v.y, 0x3E3E3E3Eu), eq4(v.z, 0x3E3E3E3Eu), eq4(v.w, 0x3E3E3E3Eu));
+        } else {
+            m = 0;
+            for (int j = 0; j < 16; j++) m |= (txt[i * 16 + j] == '>') << j;
+        }
+        while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            const size_t p = i * 16 + b;
+            if (p == 0 || txt[p - 1] == '\n') {
+                unsigned int k = atomicAdd(count, 1u);
+                if (k < cap) out[k] = (unsigned long long)p;
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < n - n16 * 16) {          // the last, partial 16 bytes
+        const size_t p = n16 * 16 + threadIdx.x;
+        if (txt[p] == '>' && (p == 0 || txt[p - 1] == '\n')) {
             unsigned int k = atomicAdd(count, 1u);
-            if (k < cap) out[k] = (unsigned long long)i;
+            if (k < cap) out[k] = (unsigned long long)p;
         }
     }
 }
@@ -149,6 +193,27 @@ __device__ void tile_kept(const uint8_t *txt, size_t n, const Spans &S, size_t t
     __syncthreads();
 }
 
+// PLAIN tiles -- the whole 4 KiB tile lies inside ONE span and holds no whitespace but newlines (every tile of an
+// ordinary FASTA except the few with a header line) -- need none of the above: a byte is kept iff it is not '\n'.
+// Each thread takes 16 bytes with one load; returns true (block-uniform) when the tile is plain, with v = the thread's
+// bytes, kept16 = its kept mask, and r = the span.  Falls back (false) on anything else, misaligned text included.
+__device__ bool tile_plain(const uint8_t *txt, size_t n, const Spans &S, size_t t0, uint4 &v, uint32_t &kept16, int &r)
+{
+    __shared__ int s_r;
+    if (t0 + FT > n || ((uintptr_t)txt & 15u)) return false;                   // (block-uniform conditions)
+    if (threadIdx.x == 0) {
+        int q = span_of(S, t0);
+        s_r = (q >= 0 && S.sbeg[q] <= t0 && S.send[q] >= t0 + FT) ? q : -1;
+    }
+    v = __ldg(reinterpret_cast<const uint4 *>(txt + t0) + threadIdx.x);
+    const uint32_t nl = pack16f(eq4(v.x, 0x0A0A0A0Au), eq4(v.y, 0x0A0A0A0Au), eq4(v.z, 0x0A0A0A0Au), eq4(v.w, 0x0A0A0A0Au));
+    const uint32_t lo = pack16f(le20_4(v.x), le20_4(v.y), le20_4(v.z), le20_4(v.w));    // every byte <= 0x20 (a superset of str whitespace)
+    kept16 = ~nl & 0xFFFFu;
+    const int odd = __syncthreads_or((lo & ~nl) != 0u);                         // also publishes s_r
+    r = s_r;
+    return r >= 0 && !odd;
+}
+
 __global__ void __launch_bounds__(FTHREADS) fasta_count_kernel(const uint8_t *txt, size_t n, Spans S, uint64_t *tile_cnt, int *err)
 {
     __shared__ uint8_t sm[FT + FHALO];
@@ -156,6 +221,25 @@ __global__ void __launch_bounds__(FTHREADS) fasta_count_kernel(const uint8_t *tx
     __shared__ int red[FTHREADS / 32];
     size_t t0 = (size_t)blockIdx.x * FT;
     __shared__ SpanCache sc;
+    {
+        uint4 v;
+        uint32_t k16;
+        int r;
+        if (tile_plain(txt, n, S, t0, v, k16, r)) {
+            int c = __popc(k16);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                int t = 0;
+                for (int w = 0; w < FTHREADS / 32; w++) t += red[w];
+                tile_cnt[blockIdx.x] = (uint64_t)t;
+            }
+            return;
+        }
+        __syncthreads();
+    }
     tile_kept(txt, n, S, t0, sm, kept, err, &sc);
     int c = 0;
     for (int i = threadIdx.x; i < FT; i += FTHREADS) c += kept[i];
@@ -219,6 +303,69 @@ __global__ void __launch_bounds__(FTHREADS) fasta_pack_kernel(const uint8_t *txt
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     size_t t0 = (size_t)blockIdx.x * FT;
     __shared__ SpanCache sc;
+    {
+        // PLAIN tile: the kept bytes are one contiguous piece of one record's sequence.  Every thread turns its 16 bytes
+        // into 3-bit codes (valid << 2 | 2-bit base), compacts the kept ones into `code` at its scan offset, and then 32
+        // bases at a time are assembled into one 32-bit half of the three plane words: a plain store when the half lies
+        // wholly inside this tile's piece, an atomicOr at the piece's two ragged ends (the planes start zeroed).
+        uint4 v;
+        uint32_t k16;
+        int r;
+        if (tile_plain(txt, n, S, t0, v, k16, r)) {
+            const int c = __popc(k16);
+            int inc = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (lane == 31) wtot[warp] = inc;
+            __syncthreads();
+            if (tid == 0) {
+                int q = 0;
+                for (int w = 0; w < FTHREADS / 32; w++) { int x = wtot[w]; wtot[w] = q; q += x; }
+                wtot[FTHREADS / 32] = q;
+            }
+            __syncthreads();
+            int pos = wtot[warp] + inc - c;
+            const uint32_t ws4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                if (!((k16 >> j) & 1u)) continue;
+                const uint32_t ch = (ws4[j >> 2] >> (8 * (j & 3))) & 255u;
+                const uint32_t x = (ch >> 1) & 3u;                                        // A 0, C 1, T 2, G 3
+                const uint32_t want = (0x47544341u >> (8u * x)) & 255u;                   // 'A','C','T','G'
+                code[pos++] = (uint8_t)(ch == want ? ((x ^ (x >> 1)) | 4u) : 0u);            // A 00 C 01 G 10 T 11; anything else: no bits
+            }
+            __syncthreads();
+            const int k = wtot[FTHREADS / 32];
+            const unsigned long long K = blk_off[r] * 64ull + (tile_excl[blockIdx.x] - pbeg[r]);   // output base index of code[0]
+            uint32_t *planes32 = reinterpret_cast<uint32_t *>(planes);
+            const unsigned long long h0 = K >> 5;                                          // first 32-base half touched
+            const int nh = (int)(((K + (unsigned long long)k + 31ull) >> 5) - h0);
+            for (int hidx = tid; hidx < nh; hidx += FTHREADS) {
+                const unsigned long long hb = h0 + (unsigned long long)hidx;               // half index: block hb >> 1, half hb & 1
+                const long long p0 = (long long)(hb << 5) - (long long)K;                  // code index of this half's bit 0
+                uint32_t hi = 0, lo = 0, va = 0;
+                const int a = p0 < 0 ? (int)-p0 : 0, b = p0 + 32 > k ? (int)(k - p0) : 32;
+                for (int j = a; j < b; j++) {
+                    const uint32_t cd = code[p0 + j];
+                    hi |= ((cd >> 1) & 1u) << j;
+                    lo |= (cd & 1u) << j;
+                    va |= (cd >> 2) << j;
+                }
+                uint32_t *dst = planes32 + (hb >> 1) * 6ull + (hb & 1ull);                 // [hi.lo32, hi.hi32, lo.lo32, lo.hi32, va.., va..]
+                if (a == 0 && b == 32) { dst[0] = hi; dst[2] = lo; dst[4] = va; }
+                else {
+                    if (hi) atomicOr(dst + 0, hi);
+                    if (lo) atomicOr(dst + 2, lo);
+                    if (va) atomicOr(dst + 4, va);
+                }
+            }
+            return;
+        }
+        __syncthreads();
+    }
     tile_kept(txt, n, S, t0, sm, kept, err, &sc);
     // each thread owns 16 consecutive bytes; block-wide exclusive scan of kept counts
     int c = 0;

@@ -208,7 +208,7 @@ def bench_score(eng, dev, n=3000, E=18_000_000):
                                                  z0.data_ptr(), dig.data_ptr(), ex.data_ptr(), w12.data_ptr(), u.data_ptr(),
                                                  v.data_ptr(), None)))
     emit('links_score (+ exact 12-digit round trip)', ms, E * (16 + 37), edges=E,
-         note='16 B/edge read, 37 B/edge written; exact '%.12g' digits from 128-bit integers (1e-8 <= x < 1e12), 320-bit route beyond')
+         note='16 B/edge read, 37 B/edge written; exact %.12g digits from 128-bit integers (1e-8 <= x < 1e12), 320-bit route beyond')
     txt = ['%.12g' % x for x in score[:200000].cpu().numpy()]
     assert (w12[:200000].cpu().numpy() == np.array([float(t) for t in txt])).all()
     scratch = torch.empty(L.salsa_scaled_scratch_bytes(2 * n) // 8 + 1, dtype=torch.int64, device=dev)
