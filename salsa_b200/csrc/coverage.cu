@@ -120,6 +120,20 @@ __device__ __forceinline__ int seg_of_chunk(const uint64_t *seg_chunk_off, int n
     return lo - 1;
 }
 
+// The four 4-element groups of a thread: warp w of a chunk owns elements [512 w, 512 w + 512) as four rows of 128, lane l the
+// 16 bytes at 4 l of every row -- 16-byte accesses, consecutive across the lanes (round 1 gave each thread 16 consecutive
+// elements: every warp load touched 32 different 128-byte lines and the two kernels were bound by the load/store unit).
+__device__ __forceinline__ int4 load_quad(const int *p, uint64_t off, int64_t e, int64_t len, bool aligned)
+{
+    if (aligned && e + 4 <= len) return *reinterpret_cast<const int4 *>(p + off + (uint64_t)e);
+    int4 x;
+    x.x = e < len ? p[off + (uint64_t)e] : 0;
+    x.y = e + 1 < len ? p[off + (uint64_t)e + 1] : 0;
+    x.z = e + 2 < len ? p[off + (uint64_t)e + 2] : 0;
+    x.w = e + 3 < len ? p[off + (uint64_t)e + 3] : 0;
+    return x;
+}
+
 __global__ void __launch_bounds__(CT) chunk_sum_kernel(const int *diff, const Seg *segs, const uint64_t *seg_chunk_off, int nseg,
                                                        unsigned long long *csum)
 {
@@ -127,15 +141,18 @@ __global__ void __launch_bounds__(CT) chunk_sum_kernel(const int *diff, const Se
     uint64_t g = blockIdx.x;
     int sg = seg_of_chunk(seg_chunk_off, nseg, g);
     Seg S = segs[sg];
-    int64_t e0 = (int64_t)(g - seg_chunk_off[sg]) * CH;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t e0 = (int64_t)(g - seg_chunk_off[sg]) * CH + warp * (CH / (CT / 32)) + lane * 4;
+    const bool al = (S.src_off & 3ull) == 0;
     long long acc = 0;
-    for (int i = threadIdx.x; i < CH; i += CT) {
-        int64_t e = e0 + i;
-        if (e < S.len) acc += diff[S.src_off + (uint64_t)e];
+#pragma unroll
+    for (int k = 0; k < PER / 4; k++) {
+        const int4 x = load_quad(diff, S.src_off, e0 + k * 128, S.len, al);
+        acc += (long long)x.x + x.y + x.z + x.w;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    if (lane == 0) red[warp] = acc;
     __syncthreads();
     if (threadIdx.x == 0) {
         long long t = 0;
@@ -149,44 +166,57 @@ __global__ void __launch_bounds__(CT) chunk_sum_kernel(const int *diff, const Se
 __global__ void __launch_bounds__(CT) chunk_scan_kernel(const int *diff, int *cov, const Seg *segs, const uint64_t *seg_chunk_off,
                                                         int nseg, const unsigned long long *cexcl, unsigned long long *seg_sum)
 {
-    __shared__ long long wsum[CT / 32];
+    __shared__ unsigned wsum[CT / 32];
     __shared__ long long red[CT / 32];
     uint64_t g = blockIdx.x;
     int sg = seg_of_chunk(seg_chunk_off, nseg, g);
     Seg S = segs[sg];
-    int64_t e0 = (int64_t)(g - seg_chunk_off[sg]) * CH + (int64_t)threadIdx.x * PER;
-    int v[PER];
-    long long run = 0;
-#pragma unroll
-    for (int j = 0; j < PER; j++) {
-        int64_t e = e0 + j;
-        v[j] = e < S.len ? diff[S.src_off + (uint64_t)e] : 0;
-        run += v[j];
-    }
-    long long inc = run;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t e0 = (int64_t)(g - seg_chunk_off[sg]) * CH + warp * (CH / (CT / 32)) + lane * 4;
+    const bool al = ((S.src_off | S.dst_off) & 3ull) == 0;
+    int4 v[PER / 4];
+    unsigned pre[PER / 4];      // sum of the warp's elements before this thread's group k (mod 2^32: the reference accumulates in int)
+    unsigned run = 0;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        long long o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += o;
+    for (int k = 0; k < PER / 4; k++) {
+        v[k] = load_quad(diff, S.src_off, e0 + k * 128, S.len, al);
+        const unsigned s = (unsigned)v[k].x + (unsigned)v[k].y + (unsigned)v[k].z + (unsigned)v[k].w;
+        unsigned inc = s;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        pre[k] = run + inc - s;
+        run += __shfl_sync(0xffffffffu, inc, 31);
     }
-    if (lane == 31) wsum[warp] = inc;
+    if (lane == 0) wsum[warp] = run;
     __syncthreads();
-    long long wb = 0;
+    unsigned wb = 0;
     for (int w = 0; w < warp; w++) wb += wsum[w];
-    long long base = (long long)(cexcl[g] - cexcl[seg_chunk_off[sg]]) + wb + inc - run;
-    if (S.seed_idx != ~0ull) base += diff[S.seed_idx];           // break_contigs.cpp:283-285: tmpcov[start-1] is the RAW diff value
+    unsigned base = (unsigned)(cexcl[g] - cexcl[seg_chunk_off[sg]]) + wb;
+    if (S.seed_idx != ~0ull) base += (unsigned)diff[S.seed_idx];  // break_contigs.cpp:283-285: tmpcov[start-1] is the RAW diff value
     long long tot = 0;
-    int c = (int)base;                                            // the reference accumulates in int
 #pragma unroll
-    for (int j = 0; j < PER; j++) {
-        int64_t e = e0 + j;
-        c += v[j];
-        if (e < S.len) { cov[S.dst_off + (uint64_t)e] = c; tot += c; }
+    for (int k = 0; k < PER / 4; k++) {
+        const int64_t e = e0 + k * 128;
+        int4 c;                                                   // the reference accumulates in int
+        c.x = (int)(base + pre[k] + (unsigned)v[k].x);
+        c.y = (int)((unsigned)c.x + (unsigned)v[k].y);
+        c.z = (int)((unsigned)c.y + (unsigned)v[k].z);
+        c.w = (int)((unsigned)c.z + (unsigned)v[k].w);
+        if (al && e + 4 <= S.len) {
+            *reinterpret_cast<int4 *>(cov + S.dst_off + (uint64_t)e) = c;
+            tot += (long long)c.x + c.y + c.z + c.w;
+        } else {
+            if (e < S.len) { cov[S.dst_off + (uint64_t)e] = c.x; tot += c.x; }
+            if (e + 1 < S.len) { cov[S.dst_off + (uint64_t)e + 1] = c.y; tot += c.y; }
+            if (e + 2 < S.len) { cov[S.dst_off + (uint64_t)e + 2] = c.z; tot += c.z; }
+            if (e + 3 < S.len) { cov[S.dst_off + (uint64_t)e + 3] = c.w; tot += c.w; }
+        }
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
-    __syncthreads();
     if (lane == 0) red[warp] = tot;
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -242,11 +272,18 @@ __device__ __forceinline__ Summ summ_shfl_down(const Summ &s, int d)
     return o;
 }
 
-// per chunk, per threshold: the monoid summary of the chunk's elements inside [lo, hi)
-__global__ void __launch_bounds__(CT) kadane_chunk_kernel(const int *cov, const Seg *segs, const uint64_t *seg_chunk_off, int nseg,
+// per chunk, per threshold: the monoid summary of the chunk's elements inside [lo, hi).
+// 64 threads per 4096-element chunk, 64 consecutive elements per thread in registers: the sequential part (about ten
+// integer instructions per element and threshold) dominates and the 8-value warp combine is paid once per 64 elements
+// (round 1: 256 threads x 16 elements, the combine cost more than the scan; and eleven int -> double conversions per
+// element: `(double)cov < cutoff` is `cov < ceil(cutoff)` for an integer cov, computed once per threshold).
+constexpr int KT = 64;            // threads per chunk in this kernel
+constexpr int KPER = CH / KT;     // 64
+
+__global__ void __launch_bounds__(KT) kadane_chunk_kernel(const int *cov, const Seg *segs, const uint64_t *seg_chunk_off, int nseg,
                                                           const unsigned long long *seg_sum, Summ *summ)
 {
-    __shared__ Summ wres[CT / 32];
+    __shared__ Summ wres[KT / 32];
     uint64_t g = blockIdx.x;
     int sg = seg_of_chunk(seg_chunk_off, nseg, g);
     Seg S = segs[sg];
@@ -255,34 +292,76 @@ __global__ void __launch_bounds__(CT) kadane_chunk_kernel(const int *cov, const 
         if (threadIdx.x < NDIV) summ[g * NDIV + threadIdx.x] = summ_empty();
         return;
     }
-    int64_t e0 = c0 + (int64_t)threadIdx.x * PER;
-    int v[PER];
+    const int64_t e0 = c0 + (int64_t)threadIdx.x * KPER;
+    // this thread's elements inside [lo, hi): j in [ja, jb)
+    const int ja = e0 >= S.lo ? 0 : (S.lo - e0 > KPER ? KPER : (int)(S.lo - e0));
+    const int jb = e0 + KPER <= S.hi ? KPER : (S.hi > e0 ? (int)(S.hi - e0) : 0);
+    int v[KPER];
+    {
+        const int4 *src = reinterpret_cast<const int4 *>(cov + S.dst_off + (uint64_t)e0);     // dst_off and e0 are multiples of 4
+        const bool whole = e0 + KPER <= S.len && ((S.dst_off & 3ull) == 0);
 #pragma unroll
-    for (int j = 0; j < PER; j++) {
-        int64_t e = e0 + j;
-        v[j] = (e >= S.lo && e < S.hi) ? cov[S.dst_off + (uint64_t)e] : 0;
+        for (int j = 0; j < KPER; j += 4) {
+            if (whole) {
+                const int4 x = src[j >> 2];
+                v[j] = x.x; v[j + 1] = x.y; v[j + 2] = x.z; v[j + 3] = x.w;
+            } else {
+#pragma unroll
+                for (int t = 0; t < 4; t++) v[j + t] = (e0 + j + t < S.len) ? cov[S.dst_off + (uint64_t)(e0 + j + t)] : 0;
+            }
+        }
     }
     // average = accumulate(cov, 0.0) / size: the sum of ints is exact in a double (< 2^53)
     const double average = (double)(long long)seg_sum[sg] / (double)S.len;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int q = 0; q < NDIV; q++) {
         const double cutoff = average / (double)(q + 5);
+        // (double)c < cutoff  <=>  c < ceil(cutoff) for an int c (never for a NaN cutoff)
+        const int ci = !(cutoff == cutoff) ? INT_MIN : (cutoff >= 2147483647.0 ? INT_MAX : (cutoff <= -2147483648.0 ? INT_MIN : (int)ceil(cutoff)));
+        const bool all_below = cutoff > 2147483647.0;     // every int is below such a cutoff
         Summ a = summ_empty();
-        int T = 0, minV = 0, minPos = (int)(e0 - 1), maxV = 0, maxPos = -1, bestV = 0, bestEnd = -1, bestStart = -1;
-        bool any = false;
+        if (jb > ja) {
+            // bestV / maxV start below every reachable value, so the first element always takes them (the reference's
+            // "first position wins ties" follows from the strict comparisons)
+            int T = 0, minV = 0, minPos = (int)(e0 + ja) - 1, maxV = INT_MIN, maxPos = -1, bestV = INT_MIN, bestEnd = -1, bestStart = -1;
+            if (ja == 0 && jb == KPER) {
+                // value and position in one word, so that every running max / min is ONE integer max / min:
+                //   Tk   = T << 14
+                //   mink = (minV << 14) + (j_min + 1)                 min: smallest T, then smallest j   (j + 1 = 0: before the thread's first element)
+                //   maxk = (maxV << 14) + (127 - j_max)               max: largest T, then smallest j
+                //   bstk = (bestV << 14) + ((127 - j_end) << 7) + (126 - j_min)   max: largest sum, then smallest end; the low 7 bits carry
+                //          the position of the prefix minimum the sum was taken from (they never decide: (bestV, j_end) is unique)
+                // Tk - mink + 127 = ((T - minV) << 14) + (126 - j_min) without a borrow, since 0 <= j_min + 1 <= 64.
+                const bool never = ci == INT_MIN && !all_below;
+                const int cm = all_below ? INT_MAX : ci - 1;              // c < ci  <=>  c <= cm   (ci > INT_MIN)
+                const int up = never ? -(1 << 14) : (1 << 14);
+                int Tk = 0, mink = 0, maxk = INT_MIN, bstk = INT_MIN;
 #pragma unroll
-        for (int j = 0; j < PER; j++) {
-            int64_t e = e0 + j;
-            if (e >= S.lo && e < S.hi) {
-                if (!any) { minPos = (int)e - 1; any = true; }
-                T += ((double)v[j] < cutoff) ? 1 : -1;           // delta +5 / -5 scaled by 1/5
-                int m = T - minV;
-                if (bestEnd < 0 || m > bestV) { bestV = m; bestEnd = (int)e; bestStart = minPos + 1; }
-                if (maxPos < 0 || T > maxV) { maxV = T; maxPos = (int)e; }
-                if (T < minV) { minV = T; minPos = (int)e; }
+                for (int j = 0; j < KPER; j++) {
+                    Tk += (v[j] <= cm) ? up : -(1 << 14);             // delta +5 / -5 scaled by 1/5
+                    bstk = max(bstk, Tk - mink + (127 + ((127 - j) << 7)));
+                    maxk = max(maxk, Tk + (127 - j));
+                    mink = min(mink, Tk + (j + 1));
+                }
+                T = Tk >> 14;
+                minV = mink >> 14; minPos = (int)e0 + (mink & 0x3FFF) - 1;
+                maxV = maxk >> 14; maxPos = (int)e0 + 127 - (maxk & 0x3FFF);
+                bestV = bstk >> 14; bestEnd = (int)e0 + 127 - ((bstk & 0x3FFF) >> 7); bestStart = (int)e0 + 126 - (bstk & 127) + 1;
+            } else {
+                for (int j = ja; j < jb; j++) {
+                    const int e = (int)e0 + j;
+                    int x = v[0];
+#pragma unroll
+                    for (int t = 1; t < KPER; t++) x = (t == j) ? v[t] : x;   // registers cannot be indexed
+                    T += (all_below || x < ci) ? 1 : -1;
+                    const int m = T - minV;
+                    if (m > bestV) { bestV = m; bestEnd = e; bestStart = minPos + 1; }
+                    if (T > maxV) { maxV = T; maxPos = e; }
+                    if (T < minV) { minV = T; minPos = e; }
+                }
             }
+            a.T = T; a.minV = minV; a.minPos = minPos; a.maxV = maxV; a.maxPos = maxPos; a.bestV = bestV; a.bestEnd = bestEnd; a.bestStart = bestStart;
         }
-        if (any) { a.T = T; a.minV = minV; a.minPos = minPos; a.maxV = maxV; a.maxPos = maxPos; a.bestV = bestV; a.bestEnd = bestEnd; a.bestStart = bestStart; }
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             Summ o = summ_shfl_down(a, d);
@@ -292,7 +371,7 @@ __global__ void __launch_bounds__(CT) kadane_chunk_kernel(const int *cov, const 
         __syncthreads();
         if (threadIdx.x == 0) {
             Summ t = wres[0];
-            for (int w = 1; w < CT / 32; w++) t = summ_combine(t, wres[w]);
+            for (int w = 1; w < KT / 32; w++) t = summ_combine(t, wres[w]);
             summ[g * NDIV + q] = t;
         }
         __syncthreads();
@@ -391,7 +470,7 @@ extern "C" int salsa_cov_analyse(const int32_t *d_diff, int32_t *d_cov, const sa
     int rc = salsa_exclusive_scan_u64((uint64_t *)d_csum, nc, st);
     if (rc) return rc;
     chunk_scan_kernel<<<(unsigned)nc, CT, 0, st>>>(d_diff, d_cov, d_segs, d_off, nseg, d_csum, d_segsum);
-    kadane_chunk_kernel<<<(unsigned)nc, CT, 0, st>>>(d_cov, d_segs, d_off, nseg, d_segsum, d_summ);
+    kadane_chunk_kernel<<<(unsigned)nc, KT, 0, st>>>(d_cov, d_segs, d_off, nseg, d_segsum, d_summ);
     kadane_final_kernel<<<(nseg * NDIV + 127) / 128, 128, 0, st>>>(d_summ, d_off, nseg, d_rs, d_re);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(h_sum, d_segsum, (size_t)nseg * 8, cudaMemcpyDeviceToHost, st));
