@@ -481,7 +481,9 @@ int salsa_break_contigs_run(int32_t joins, int32_t argc, const char *const *argv
  *     number found, which may exceed `capacity` -- then grow and repeat.
  *     Data errors (missing fields or '/', bad integers) land in d_stats as
  *     for the ingest; the reference raises IndexError / ValueError there.
- *  2. salsa_sort_u64 (CUB) puts them in file order = output order.
+ *  2. salsa_sort_u64 (CUB) puts them in file order = output order; max_key
+ *     (0 = unknown) bounds the keys, so that only the bits a key can have
+ *     are sorted (offsets into a 10 GB BED: 34 bits, 5 radix passes of 8).
  *  3. salsa_reproject_emit works in blocks of 256 consecutive candidates
  *     (nblk = salsa_reproject_blocks(ncand)).  With d_out == NULL it writes
  *     each candidate's output byte count to d_len[ncand] and each block's to
@@ -493,7 +495,7 @@ int salsa_break_contigs_run(int32_t joins, int32_t argc, const char *const *argv
 int salsa_reproject_candidates(salsa_ctx *ctx, const void *d_bed, size_t nbytes, int32_t refactor,
                                const int32_t *d_scaffold_of, uint64_t *d_cand, size_t capacity,
                                uint64_t *d_count, uint64_t *d_stats, void *stream);
-int salsa_sort_u64(uint64_t *d_in, uint64_t *d_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream);
+int salsa_sort_u64(uint64_t *d_in, uint64_t *d_out, size_t n, uint64_t max_key, void *d_tmp, size_t *tmp_bytes, void *stream);
 size_t salsa_reproject_blocks(size_t ncand);
 int salsa_reproject_emit(salsa_ctx *ctx, const void *d_bed, size_t nbytes, int32_t refactor,
                          const uint64_t *d_cand, size_t ncand, const int32_t *d_scaffold_of,

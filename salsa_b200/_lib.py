@@ -79,7 +79,7 @@ SIGNATURES = {
     'salsa_break_contigs_run': (C.c_int, [c_i32, c_i32, c_void_p, c_void_p, c_size_t, C.c_char_p]),
     'salsa_reproject_candidates': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_void_p, c_void_p, c_size_t, c_void_p,
                                              c_void_p, c_void_p]),
-    'salsa_sort_u64': (C.c_int, [c_void_p, c_void_p, c_size_t, c_void_p, C.POINTER(c_size_t), c_void_p]),
+    'salsa_sort_u64': (C.c_int, [c_void_p, c_void_p, c_size_t, C.c_uint64, c_void_p, C.POINTER(c_size_t), c_void_p]),
     'salsa_reproject_blocks': (c_size_t, [c_size_t]),
     'salsa_reproject_emit': (C.c_int, [c_void_p, c_void_p, c_size_t, c_i32, c_void_p, c_size_t] + [c_void_p] * 9 +
                              [c_size_t, c_void_p, c_void_p]),

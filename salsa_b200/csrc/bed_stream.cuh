@@ -454,6 +454,9 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
 
     // ---- phase 2: nb (<= 16) queued pairs, two lanes per pair ----
     auto flush = [&](uint32_t nb) {
+#if defined(SALSA_ABL) && SALSA_ABL == 1          // timing experiments only (tools/sweep_stream.sh): phase 2 dropped
+        qh += nb; qn -= nb; return;
+#endif
         const uint32_t ei = (uint32_t)lane >> 1, role = (uint32_t)lane & 1u;    // role 0: the pair's current line, 1: its previous line
         const bool act = ei < nb;
         uint4 e = make_uint4(0, 0, 0, 0);
@@ -517,6 +520,9 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
             uint32_t diff = L.rlen ^ orl;
             const uint32_t *rp = gwords(gsrc, r0);
             const uint32_t rsh = ((uint32_t)r0 & 3u) * 8u;
+#if defined(SALSA_ABL) && SALSA_ABL == 3          // (3: no read-name comparison)
+            if (0)
+#endif
             for (uint32_t j = 0; j < nwmax; j++) {
                 uint32_t w = 0;
                 if (j < nw) {
@@ -560,7 +566,9 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
                 if (oid < L.id) { first = (uint32_t)oid; second = (uint32_t)L.id; ends = ep * 2u + ec; }
                 else { first = (uint32_t)L.id; second = (uint32_t)oid; ends = ec * 2u + ep; }
                 const uint64_t key = (((uint64_t)first * (uint64_t)A.t.n + second) << 2) | ends;
+#if !defined(SALSA_ABL) || SALSA_ABL != 2         // (2: everything but the RED into the table)
                 Emit::emit(EA, A, key, line_off);
+#endif
                 npairs++;
             }
         }

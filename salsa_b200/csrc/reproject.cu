@@ -338,15 +338,18 @@ extern "C" int salsa_reproject_candidates(salsa_ctx *ctx, const void *d_bed, siz
     return bedscan::launch_scan<CandPolicy<false>>(C, t, d_bed, nbytes, 0, d_stats, as_stream(stream));
 }
 
-extern "C" int salsa_sort_u64(uint64_t *d_in, uint64_t *d_out, size_t n, void *d_tmp, size_t *tmp_bytes, void *stream)
+extern "C" int salsa_sort_u64(uint64_t *d_in, uint64_t *d_out, size_t n, uint64_t max_key, void *d_tmp, size_t *tmp_bytes, void *stream)
 {
     if (!tmp_bytes) SALSA_FAIL(SALSA_ERR_ARG, "tmp_bytes is NULL");
     if (n > 0x7fffffffull) SALSA_FAIL(SALSA_ERR_ARG, "too many keys to sort");
+    // only the bits a key can have are sorted: line offsets of a 10 GB BED need 34, which is 5 radix passes instead of 8
+    int bits = 64;
+    if (max_key) { bits = 1; while (bits < 64 && (max_key >> bits)) bits++; }
     size_t need = 0;
-    CUDA_TRY(cub::DeviceRadixSort::SortKeys(NULL, need, d_in, d_out, (int)n, 0, 64, as_stream(stream)));
+    CUDA_TRY(cub::DeviceRadixSort::SortKeys(NULL, need, d_in, d_out, (int)n, 0, bits, as_stream(stream)));
     if (!d_tmp) { *tmp_bytes = need; return SALSA_OK; }
     if (*tmp_bytes < need) SALSA_FAIL(SALSA_ERR_ARG, "sort scratch too small: need %zu", need);
-    CUDA_TRY(cub::DeviceRadixSort::SortKeys(d_tmp, need, d_in, d_out, (int)n, 0, 64, as_stream(stream)));
+    CUDA_TRY(cub::DeviceRadixSort::SortKeys(d_tmp, need, d_in, d_out, (int)n, 0, bits, as_stream(stream)));
     return SALSA_OK;
 }
 

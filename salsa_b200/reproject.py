@@ -190,9 +190,9 @@ def reproject(eng, bed, refactor, scaffold_of, offset, length, reversed_, scaf_n
         return torch.empty(0, dtype=torch.uint8, device=dev)
     srt = torch.empty(n, dtype=torch.int64, device=dev)
     tb = C.c_size_t(0)
-    check(L.salsa_sort_u64(cand.data_ptr(), srt.data_ptr(), n, None, C.byref(tb), st))
+    check(L.salsa_sort_u64(cand.data_ptr(), srt.data_ptr(), n, bed.numel(), None, C.byref(tb), st))
     tmp = torch.empty(tb.value + 16, dtype=torch.uint8, device=dev)
-    check(L.salsa_sort_u64(cand.data_ptr(), srt.data_ptr(), n, tmp.data_ptr(), C.byref(tb), st))
+    check(L.salsa_sort_u64(cand.data_ptr(), srt.data_ptr(), n, bed.numel(), tmp.data_ptr(), C.byref(tb), st))
     del cand, tmp
     nblk = L.salsa_reproject_blocks(n)
     lens = torch.empty(n, dtype=torch.int32, device=dev)

@@ -29,12 +29,49 @@ def run(bin_dir, data, out, extra):
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
     wall = time.time() - t0
-    steps = {}
+    steps, per_iter = {}, []
     for ln in open(out + '/timings.tsv'):
         k, v = ln.split('\t')
+        if '--verbose' in sys.argv:
+            sys.stderr.write('  %-24s %8.3f s\n' % (k, float(v)))
         steps[k] = steps.get(k, 0.0) + float(v)
+        if k == 'make_links.py':                      # every iteration opens with it (run_pipeline.py:271-385)
+            per_iter.append({})
+        if per_iter and k in ITER_STEPS:
+            per_iter[-1][k] = per_iter[-1].get(k, 0.0) + float(v)
     iters = len([f for f in os.listdir(out) if f.startswith('contig_links_iteration_')])
+    run.per_iteration = per_iter
     return wall, steps, iters
+
+
+ITER_STEPS = ('make_links.py', 'fast_scaled_scores.py', 'layout_unitigs.py', 'break_contigs', 'refactor_breaks.py')
+
+
+def cpu_sample(data, gpu_out, work, nlines):
+    """The CPU path's seconds for the hot steps of ONE iteration on the first `nlines` lines of the same BED: the
+    oracle's C port of make_links + fast_scaled_scores (1 thread) and the compiled reference break_contigs_start."""
+    import oracle
+    oracle.build()
+    obin = pu.make_oracle_bin(work + '/obin')
+    os.makedirs(work + '/cpu', exist_ok=True)
+    sample = work + '/sample.bed'
+    with open(data + '/reads.bed', 'rb') as f, open(sample, 'wb') as g:
+        for i, ln in enumerate(f):
+            if i >= nlines:
+                break
+            g.write(ln)
+    for nm in ('scaffold_length_iteration_1', 're_counts_iteration_1'):
+        os.symlink(os.path.join(gpu_out, nm), os.path.join(work, 'cpu', nm))
+    out = {'sample': 'first %d lines of the same BED; oracle C port (1 thread), compiled reference break_contigs_start' % nlines,
+           'lines': nlines}
+    for key, cmd in (('make_links.py', [sys.executable, obin + '/make_links.py', '-b', sample, '-d', work + '/cpu', '-i', '1']),
+                     ('fast_scaled_scores.py', [sys.executable, obin + '/fast_scaled_scores.py', '-d', work + '/cpu', '-i', '1']),
+                     ('break_contigs_start', [obin + '/break_contigs_start', '-a', sample, '-l', data + '/contigs.len', '-s', '100'])):
+        t0 = time.time()
+        r = subprocess.run(cmd, capture_output=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        out[key] = round(time.time() - t0, 3)
+    return out
 
 
 def main():
@@ -54,9 +91,21 @@ def main():
         shape = 'BASELINE configs[0]: 2 Mb genome, 200 contigs, %d pairs, %s' % (pairs, ' '.join(args))
     wg, sg, ig = run(pu.BIN, data, d + '/gpu', args)
     if '--gpu-only' in sys.argv:
-        print(json.dumps({'metric': 'seconds_per_pipeline_iteration', 'config': shape, 'pairs': pairs, 'iterations_run': ig,
-                          'gpu_path': {'wall_s': wg, 'startup_s': sg.get('startup', 0.0),
-                                       's_per_iteration_after_startup': (sum(sg.values()) - sg.get('startup', 0.0)) / ig, 'steps_s': sg}}))
+        per = run.per_iteration
+        rec = {'metric': 'seconds_per_pipeline_iteration', 'config': shape, 'pairs': pairs, 'iterations_run': ig,
+               'first_iteration_s': round(sum(per[0].values()), 3) if per else None,
+               'mean_iteration_s': round(sum(sum(p.values()) for p in per) / max(1, len(per)), 3),
+               'per_iteration_steps_s': [{k: round(v, 3) for k, v in p.items()} for p in per],
+               'gpu_path': {'wall_s': wg, 'startup_s': sg.get('startup', 0.0), 'steps_s': sg},
+               'note': 'one iteration = make_links -> fast_scaled_scores (+ sort) -> layout_unitigs -> break_contigs -> '
+                       'refactor_breaks (run_pipeline.py:271-385); the first one reads the whole input BED, later ones the '
+                       're-projected BED, which shrinks as contigs join'}
+        if '--cpu-sample' in sys.argv:
+            rec['cpu_path'] = cpu_sample(data, d + '/gpu', d, int(sys.argv[sys.argv.index('--cpu-sample') + 1]))
+        print(json.dumps(rec))
+        if '--keep' not in sys.argv:
+            import shutil
+            shutil.rmtree(d, ignore_errors=True)
         return
     import oracle
     oracle.build()

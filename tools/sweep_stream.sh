@@ -5,7 +5,7 @@ cd "$(dirname "$0")/.."
 for flags in "$@"; do
     make -C salsa_b200/csrc -s clean >/dev/null 2>&1
     make -C salsa_b200/csrc -s -j8 NVFLAGS_EXTRA="$flags" >/dev/null 2>&1 || { echo "{\"flags\": \"$flags\", \"error\": \"build failed\"}"; continue; }
-    r=$(python bench.py --steps 5 --warmup 3 --no-extras 2>/dev/null | tail -1)
+    r=$(SALSA_BENCH_ABLATION=$ABL python bench.py --steps 5 --warmup 3 --no-extras 2>/dev/null | tail -1)
     echo "{\"flags\": \"$flags\", \"result\": $r}"
 done
 make -C salsa_b200/csrc -s clean >/dev/null 2>&1
