@@ -16,16 +16,32 @@ import torch
 import torch.distributed as dist
 
 
-def shard_ranges(view, world):
+def shard_ranges(view, world, involved=None):
     """Cut a BED (anything indexable as bytes: bytes, np.memmap, ...) into `world`
     byte ranges that start on line starts and overlap by exactly one line, the
     chunking rule of salsa_bed_ingest_dense (include/salsa_b200.h): shard k's first
     line is shard k-1's last line, which only plays "previous"
     (make_links.py:66-68), so every adjacent-line pair is evaluated exactly once.
+    involved: with an avoid list (iterations >= 2) the set of contig names that occur
+    in some avoid pair (Engine.involved, as bytes).  The reference's `continue`
+    leaves prev_line stale across skipped pairs (make_links.py:72-74), so a shard
+    may only start on a line that can never be skipped -- one whose contig is in no
+    avoid pair; the cut walks back to such a line (as Engine.ingest_file does).
     Returns [(lo, hi)] * world; empty shards are (hi, hi)."""
     n = len(view)
     if n == 0:
         return [(0, 0)] * world
+    if involved is not None:
+        involved = set(x if isinstance(x, bytes) else str(x).encode('latin-1') for x in involved)
+
+    def free_line_at_or_before(p, floor):
+        # the last line start <= p whose contig is in no avoid pair (floor if there is none after it)
+        while p > floor:
+            tok = bytes(view[p:min(n, p + 1024)]).split(None, 1)
+            if not tok or tok[0] not in involved:
+                return p
+            p = line_start_at_or_before(p - 1)
+        return floor
 
     def line_start_at_or_before(p):
         # start of the line that contains byte p
@@ -41,7 +57,10 @@ def shard_ranges(view, world):
     cuts = [0]
     for k in range(1, world):
         p = n * k // world
-        cuts.append(max(cuts[-1], line_start_at_or_before(min(p, n - 1))))
+        c = max(cuts[-1], line_start_at_or_before(min(p, n - 1)))
+        if involved:
+            c = free_line_at_or_before(c, cuts[-1])
+        cuts.append(c)
     ranges = []
     for k in range(world):
         lo = cuts[k]

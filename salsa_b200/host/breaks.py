@@ -89,5 +89,12 @@ def refactor(directory, iteration, bed_pass, re_pass=None):
     with open('%s/scaffolds_iteration_%d.p' % (directory, iteration - 1), 'wb') as f:
         pickle.dump(new, f)
     reproject.update_bed(directory, new, unitig_length, iteration, refactor=True, bed_pass=bed_pass, re_pass=re_pass)
-    open('%s/misasm_%d.DONE' % (directory, iteration), 'w').close()
+    # DONE vouches for a complete alignment_iteration_N.bed (refactor_breaks.py writes the BED, then the marker): a pass
+    # that writes the BED behind the pipeline's back creates the marker itself, behind the finished file
+    marker = '%s/misasm_%d.DONE' % (directory, iteration)
+    after = getattr(bed_pass, 'after_write', None)
+    if after is not None:
+        after('%s/alignment_iteration_%d.bed' % (directory, iteration), marker)
+    else:
+        open(marker, 'w').close()
     return new

@@ -19,7 +19,9 @@ from .engine import _blob
 
 CHUNK = 64 << 20
 _RESIDENT = {}          # realpath -> (size, mtime_ns, uint8 CUDA tensor); size None while the file is still being written
-_WRITERS = {}           # realpath -> _Writer still running
+_WRITERS = {}           # realpath -> _Writer still running (a writer takes itself out when its file is complete)
+_FAILED = {}            # realpath -> exception of a writer that failed; raised by flush()
+_LOCK = threading.Lock()
 
 
 def resident_bed(path, device, load=True):
@@ -77,6 +79,7 @@ class _Writer(threading.Thread):
     def __init__(self, rp, t, ready):
         super().__init__(daemon=True)
         self.rp, self.t, self.ready, self.cancelled, self.error = rp, t, ready, False, None
+        self.markers, self.done = [], False          # files to create once the BED is complete on disk (after_write)
 
     def run(self):
         try:
@@ -107,41 +110,70 @@ class _Writer(threading.Thread):
                 os.replace(self.rp + '.part', self.rp)
         except Exception as e:           # reported by flush()
             self.error = e
+        # The file is complete (or abandoned): the writer lets go of the tensor and of its place in _WRITERS, so that
+        # _remember can drop the product once a newer one exists; markers appear only behind a complete file.
+        with _LOCK:
+            self.done = True
+            if _WRITERS.get(self.rp) is self:
+                del _WRITERS[self.rp]
+            if self.error is not None:
+                _FAILED[self.rp] = self.error
+            elif not self.cancelled:
+                hit = _RESIDENT.get(self.rp)
+                if hit is not None and hit[0] is None and hit[2] is self.t:
+                    st = os.stat(self.rp)
+                    _RESIDENT[self.rp] = (st.st_size, st.st_mtime_ns, hit[2])
+                for m in self.markers:
+                    open(m, 'w').close()
+            self.t = None
 
 
 def write_behind(path, t):
     """Start writing t to `path` in the background; t stays the resident copy of that file.  A write of the
     same path that is still running is abandoned (its content is about to be replaced)."""
     rp = os.path.realpath(path)
-    old = _WRITERS.pop(rp, None)
+    old = _WRITERS.get(rp)
     if old is not None:
         old.cancelled = True
         old.join()
+    _FAILED.pop(rp, None)
     if os.path.lexists(rp):
         os.remove(rp)
     ready = torch.cuda.Event()
     ready.record()
     w = _Writer(rp, t, ready)
-    _WRITERS[rp] = w
-    _remember(rp, None, None, t)
+    with _LOCK:
+        _WRITERS[rp] = w
+        _remember(rp, None, None, t)
     w.start()
+
+
+def after_write(path, marker):
+    """Create the (empty) file `marker` once `path` is complete on disk: right away when nothing is writing it any more,
+    else from the writer thread behind its rename -- a DONE marker never precedes the BED it vouches for."""
+    rp = os.path.realpath(path)
+    with _LOCK:
+        w = _WRITERS.get(rp)
+        if w is not None and not w.done:
+            w.markers.append(marker)
+            return
+    err = _FAILED.pop(rp, None)
+    if err is not None:
+        raise err
+    open(marker, 'w').close()
 
 
 def flush(path=None):
     """Wait until the file(s) this process is writing are complete on disk (all of them when path is None).
     Must precede anything outside this process that reads them."""
-    keys = [os.path.realpath(path)] if path is not None else list(_WRITERS)
+    keys = [os.path.realpath(path)] if path is not None else list(dict.fromkeys(list(_WRITERS) + list(_FAILED)))
     for rp in keys:
-        w = _WRITERS.pop(rp, None)
-        if w is None:
-            continue
-        w.join()
-        if w.error is not None:
-            raise w.error
-        hit = _RESIDENT.get(rp)
-        if hit is not None and hit[0] is None:
-            st = os.stat(rp)
-            _RESIDENT[rp] = (st.st_size, st.st_mtime_ns, hit[2])
+        w = _WRITERS.get(rp)
+        if w is not None:
+            w.join()
+        err = _FAILED.pop(rp, None)
+        if err is not None:
+            raise err
 
 
 def _remember(rp, size, mtime_ns, t):
@@ -376,4 +408,5 @@ def bed_pass(eng, background=False, chunk_bytes=None):
         write_behind(dst, out)
         if not background:
             flush(dst)
+    run.after_write = after_write
     return run

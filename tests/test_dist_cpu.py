@@ -55,6 +55,44 @@ def test_shard_ranges_cover_every_pair_once(oracle_lib):
     assert sum(hi - lo for lo, hi in shard_ranges(one_line, 4)) >= len(one_line)
 
 
+def test_shard_ranges_with_an_avoid_list(oracle_lib):
+    """Iterations >= 2: a skipped (avoid-listed) pair leaves the reference's prev_line stale (make_links.py:72-74), so
+    a shard may only start on a line whose contig is in no avoid pair; with `involved` the cuts walk back to one and
+    the shards' links add up to the whole file's."""
+    from salsa_b200 import synth
+    from salsa_b200.dist import shard_ranges
+    asm, rec, bed = synth.small_case(ncontig=12, genome=300_000, npairs=6000, seed=21, triple=0.1, noise=0.5)
+    n = asm.ncontig
+    one = np.ones(n, np.int64)
+    avoid = [(asm.names[i], asm.names[j]) for i, j in ((0, 1), (1, 2), (2, 3), (3, 4), (5, 6), (6, 7), (7, 8), (9, 0))]
+    involved = set(x for pr in avoid for x in pr)
+
+    def links(b):
+        r = oracle_lib.make_links(b, asm.names, asm.lengths.astype(float), np.ones(n, np.uint8), one, one, avoid=avoid)
+        return {(int(a), int(c), int(e)): int(k) for a, c, e, k in zip(r['first'], r['second'], r['ends'], r['count'])}
+
+    whole = links(bed)
+    assert whole
+    differs = False
+    for world in (2, 3, 8):
+        ranges = shard_ranges(bed, world, involved=involved)
+        assert len(ranges) == world and ranges[0][0] == 0 and ranges[-1][1] == len(bed)
+        merged = {}
+        for lo, hi in ranges:
+            assert lo == 0 or bed[lo - 1:lo] == b'\n'
+            assert lo == 0 or bed[lo:lo + 64].split(None, 1)[0] not in involved
+            for k, v in links(bed[lo:hi]).items():
+                merged[k] = merged.get(k, 0) + v
+        assert merged == whole, world
+        # the cuts that ignore the avoid list are the wrong ones here (that is what the parameter is for)
+        naive = {}
+        for lo, hi in shard_ranges(bed, world):
+            for k, v in links(bed[lo:hi]).items():
+                naive[k] = naive.get(k, 0) + v
+        differs = differs or naive != whole
+    assert differs
+
+
 def test_fasta_shards_and_merge(oracle_lib):
     """RE counting shards by contig: byte ranges cut at record headers, each counted on its own (here by the oracle),
     merged with the reference's dict semantics -- equal to counting the whole file, for any number of ranks."""
