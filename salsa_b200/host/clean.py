@@ -33,8 +33,10 @@ def read_fasta(path):
         return {}
     if data[:1] != b'>':
         return _read_fasta_lines(path)
-    a = np.frombuffer(data, dtype=np.uint8)
-    starts = np.concatenate(([0], np.flatnonzero((a[1:] == 62) & (a[:-1] == 10)) + 1)).tolist()
+    starts, q = [0], data.find(b'\n>')
+    while q >= 0:
+        starts.append(q + 1)
+        q = data.find(b'\n>', q + 1)
     starts.append(len(data))
     fa = {}
     for b, e in zip(starts[:-1], starts[1:]):
@@ -43,8 +45,25 @@ def read_fasta(path):
         body = data[nl + 1:e] if nl >= 0 else b''
         if not head.split() or any(c in body for c in (b' ', b'\t', b'\r', b'\x0b', b'\x0c')) or b'\r' in head:
             return _read_fasta_lines(path)
-        fa[head.decode('latin-1').rstrip().split()[0]] = body.translate(None, b'\n').decode('latin-1')
+        fa[head.decode('latin-1').rstrip().split()[0]] = _unwrap(body).decode('latin-1')
     return fa
+
+
+def _unwrap(body):
+    """body without its newlines.  Evenly wrapped records (every line but the last as wide as the first) are a
+    strided copy; anything else goes through bytes.translate."""
+    w = body.find(b'\n')
+    if w <= 0:
+        return body.translate(None, b'\n')
+    k = len(body) // (w + 1)
+    tail = body[k * (w + 1):]
+    tn = tail.count(b'\n')
+    if tn > 1 or (tn == 1 and tail[-1:] != b'\n') or body.count(b'\n') != k + tn:
+        return body.translate(None, b'\n')
+    a = np.frombuffer(body, dtype=np.uint8, count=k * (w + 1)).reshape(k, w + 1)
+    if not (a[:, w] == 10).all():
+        return body.translate(None, b'\n')
+    return a[:, :w].copy().tobytes() + tail.rstrip(b"\n")
 
 
 def wrap_fasta(s, width=80):
