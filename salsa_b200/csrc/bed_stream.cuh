@@ -462,6 +462,9 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         uint4 e = make_uint4(0, 0, 0, 0);
         if (act) e = queue[(qh + ei) & (QCAP - 1)];
         const uint32_t st = role ? e.y : e.x, P = role ? e.w : e.z;
+#if defined(SALSA_ABL) && SALSA_ABL == 4          // (4: the queue is read, nothing else)
+        npairs += e.x & 1u; qh += nb; qn -= nb; __syncwarp(); return;
+#endif
         LineInfo L;
         L.id = -1; L.info = 0; L.noff = L.roff = 0; L.nlen = L.rlen = 0;
         long long sum = 0;
@@ -506,6 +509,9 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
             L.info |= ((m.flags & SALSA_CTG_HAS_LEN) ? 32u : 0u) | ((m.flags & SALSA_CTG_HAS_RE) ? 64u : 0u) |
                       (m.len_floor == 0 ? 128u : 0u) | (sum > m.len_floor ? 256u : 0u);
         }
+#if defined(SALSA_ABL) && SALSA_ABL == 5          // (5: both lines parsed and looked up, nothing else)
+        npairs += (uint32_t)(L.id + (int)sum + (int)L.info) & 1u; qh += nb; qn -= nb; __syncwarp(); return;
+#endif
         // ---- read.split('/')[0] of both lines (make_links.py:78) ----
         const uint32_t oinfo = __shfl_xor_sync(0xffffffffu, L.info, 1);
         const int oid = __shfl_xor_sync(0xffffffffu, L.id, 1);

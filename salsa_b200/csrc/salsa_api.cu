@@ -184,7 +184,11 @@ extern "C" int salsa_names_build(salsa_ctx *c, const char *blob, const int64_t *
     if (off[n] >= (int64_t)1 << 32) SALSA_FAIL(SALSA_ERR_ARG, "name blob too large");
     free_table(c);
     uint32_t nslots = 64;
-    while (nslots < (uint32_t)n * 2u + 2u) nslots <<= 1;
+    // Sparse on purpose: a second probe of one lane is a second L2 round trip (and a divergent loop) for the whole warp of
+    // the scanner's phase 2 (bed_stream.cuh), and with 32 lookups per batch "some lane collides" is the rule at the usual
+    // load of 0.5 (measured on B200, 3,000 contigs: 22.0 ms per 47 GB step at load 0.37, 21.4 at 0.09, 21.0 at 0.01).
+    // 64 slots per name up to 2^20 slots (32 MB, stays in L2); beyond that at least 2 per name.
+    while ((nslots < (uint32_t)n * 64u + 2u && nslots < (1u << 20)) || nslots < (uint32_t)n * 2u + 2u) nslots <<= 1;
     std::vector<NameSlot> slots(nslots);
     for (auto &s : slots) {
         memset(&s, 0, sizeof s);
