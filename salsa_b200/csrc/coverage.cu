@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(KT) kadane_chunk_kernel(const int *cov, const 
             // bestV / maxV start below every reachable value, so the first element always takes them (the reference's
             // "first position wins ties" follows from the strict comparisons)
             int T = 0, minV = 0, minPos = (int)(e0 + ja) - 1, maxV = INT_MIN, maxPos = -1, bestV = INT_MIN, bestEnd = -1, bestStart = -1;
-            if (ja == 0 && jb == KPER) {
+            if (ja == 0 && jb == KPER && (all_below || ci != INT_MIN)) {      // (a cutoff no int is below: the loop further down)
                 // value and position in one word, so that every running max / min is ONE integer max / min:
                 //   Tk   = T << 14
                 //   mink = (minV << 14) + (j_min + 1)                 min: smallest T, then smallest j   (j + 1 = 0: before the thread's first element)
@@ -332,17 +332,19 @@ __global__ void __launch_bounds__(KT) kadane_chunk_kernel(const int *cov, const 
                 //   bstk = (bestV << 14) + ((127 - j_end) << 7) + (126 - j_min)   max: largest sum, then smallest end; the low 7 bits carry
                 //          the position of the prefix minimum the sum was taken from (they never decide: (bestV, j_end) is unique)
                 // Tk - mink + 127 = ((T - minV) << 14) + (126 - j_min) without a borrow, since 0 <= j_min + 1 <= 64.
-                const bool never = ci == INT_MIN && !all_below;
-                const int cm = all_below ? INT_MAX : ci - 1;              // c < ci  <=>  c <= cm   (ci > INT_MIN)
-                const int up = never ? -(1 << 14) : (1 << 14);
+                const int cm = all_below ? INT_MAX : ci - 1;              // c < ci  <=>  c <= cm   (ci > INT_MIN: see the branch above)
+                constexpr int UP = 1 << 14;
+                // Tk holds T << 14 minus (j + 1) * UP, the part every element adds anyway: an element that is NOT below the
+                // cutoff then costs one predicated subtraction, and the (j + 1) * UP goes into the constants below
                 int Tk = 0, mink = 0, maxk = INT_MIN, bstk = INT_MIN;
 #pragma unroll
                 for (int j = 0; j < KPER; j++) {
-                    Tk += (v[j] <= cm) ? up : -(1 << 14);             // delta +5 / -5 scaled by 1/5
-                    bstk = max(bstk, Tk - mink + (127 + ((127 - j) << 7)));
-                    maxk = max(maxk, Tk + (127 - j));
-                    mink = min(mink, Tk + (j + 1));
+                    if (v[j] > cm) Tk -= 2 * UP;                      // delta +5 / -5 scaled by 1/5
+                    bstk = max(bstk, Tk - mink + ((j + 1) * UP + 127 + ((127 - j) << 7)));
+                    maxk = max(maxk, Tk + ((j + 1) * UP + (127 - j)));
+                    mink = min(mink, Tk + ((j + 1) * UP + (j + 1)));
                 }
+                Tk += KPER * UP;
                 T = Tk >> 14;
                 minV = mink >> 14; minPos = (int)e0 + (mink & 0x3FFF) - 1;
                 maxV = maxk >> 14; maxPos = (int)e0 + 127 - (maxk & 0x3FFF);
