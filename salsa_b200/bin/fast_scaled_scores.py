@@ -125,23 +125,23 @@ def scaled_from_arrays(eng, node_names, u, v, w, links, want_sorted=False):
     from salsa_b200.engine import _blob
     blob, off = _blob(node_names)
     cap = n * 160 + 2 * int(np.diff(off)[u].sum() + np.diff(off)[v].sum()) + 1024
-    out = C.create_string_buffer(cap)
+    out = np.empty(cap, dtype=np.uint8)                            # (create_string_buffer would zero it, .raw would copy all of it)
     c = lambda a, t: np.ascontiguousarray(a, t)                    # noqa: E731
     arrs = [c(u, np.int32), c(v, np.int32), c(wd, np.int64), c(wk, np.int32), c(res['b_digits'], np.int64),
             c(res['b_exp10'], np.int32), c(res['is_int1'], np.uint8), c(res['r_digits'], np.int64),
             c(res['r_exp10'], np.int32), c(links, np.int64)]
-    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], n, out, cap)
+    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], n, out.ctypes.data, cap)
     if nb < 0:
         raise RuntimeError(eng.L.salsa_last_error().decode())
+    text = out[:nb].tobytes()
     if not want_sorted:
-        return out.raw[:nb]
-    text = out.raw[:nb]
+        return text
     perm = sort_order(eng, node_names, u, v, res['r_digits'], res['r_exp10'])
     arrs = [np.ascontiguousarray(a[perm]) for a in arrs]
-    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], n, out, cap)
+    nb = eng.L.salsa_format_scaled(blob, off.ctypes.data, *[a.ctypes.data for a in arrs], n, out.ctypes.data, cap)
     if nb < 0:
         raise RuntimeError(eng.L.salsa_last_error().decode())
-    return text, out.raw[:nb]
+    return text, out[:nb].tobytes()
 
 
 def main(argv=None):

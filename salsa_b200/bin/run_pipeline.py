@@ -166,7 +166,20 @@ def _main(argv=None):
             redirect = words[words.index('>') + 1]
             words = words[:words.index('>')]
         if inproc and words[0] == py and step.endswith('.py'):
+            prof_dir = os.environ.get('SALSA_PROFILE_STEPS')       # development aid: cProfile of every in-process step
+            if prof_dir:
+                import cProfile
+                import io
+                import pstats
+                pr = cProfile.Profile()
+                pr.enable()
             rc, errtext = run_inprocess(words, redirect), ''
+            if prof_dir:
+                pr.disable()
+                buf = io.StringIO()
+                pstats.Stats(pr, stream=buf).sort_stats('cumtime').print_stats(28)
+                modules['nprof'] = modules.get('nprof', 0) + 1
+                open(os.path.join(prof_dir, '%02d_%s.txt' % (modules['nprof'], step)), 'w').write(buf.getvalue())
         elif inproc and step in ('break_contigs', 'break_contigs_start'):
             rc, errtext = run_coverage_inprocess(step, words, redirect), ''
         else:

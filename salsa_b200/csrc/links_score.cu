@@ -13,7 +13,10 @@
 // (round-half-even on the exact binary value, like glibc/CPython) and the
 // correctly rounded double of D*10^(k-11).  The host only assembles text from
 // (D, k); it never converts a float.
+#include <memory>
 #include <mutex>
+#include <thread>
+#include <vector>
 
 #include "common.cuh"
 
@@ -572,32 +575,85 @@ extern "C" int salsa_format_g12(const int64_t *h_digits, const int32_t *h_exp10,
     return SALSA_OK;
 }
 
+// The two file formatters below run on all host threads: lines are independent, so the edge range is cut into one
+// contiguous piece per thread, every piece is written into its own buffer, and the pieces are copied behind one another
+// (11 M link lines took 0.4 s per call on one thread -- the largest single item of a pipeline iteration's first pass).
+// fmt(lo, hi, dst, cap) -> bytes written, or -(index + 1) of the first edge it cannot write / -(n + 1) for "buffer too small".
+template <class F>
+static int64_t format_parallel(size_t n, char *out, size_t out_cap, size_t line_bound, const F &fmt, const char *who)
+{
+    unsigned hw = std::thread::hardware_concurrency();
+    size_t T = hw ? hw : 1;
+    if (T > 32) T = 32;
+    if (T > n / 32768 + 1) T = n / 32768 + 1;
+    if (T <= 1) {
+        int64_t r = fmt(0, n, out, out_cap);
+        if (r == -(int64_t)(n + 1)) { salsa_set_error("%s: buffer too small", who); return -1; }
+        if (r < 0) { salsa_set_error("%s: a value of edge %zu lies outside [1e-30, 1e30]", who, (size_t)(-r - 1)); return -1; }
+        return r;
+    }
+    std::vector<std::unique_ptr<char[]>> buf(T);        // not value-initialised: the pieces are written, never read before
+    std::vector<int64_t> got(T, 0);
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < T; t++)
+        th.emplace_back([&, t]() {
+            const size_t lo = n * t / T, hi = n * (t + 1) / T;
+            const size_t cap = (hi - lo) * line_bound + 64;
+            buf[t].reset(new char[cap]);
+            got[t] = fmt(lo, hi, buf[t].get(), cap);
+        });
+    for (auto &x : th) x.join();
+    size_t total = 0;
+    for (size_t t = 0; t < T; t++) {
+        if (got[t] == -(int64_t)(n + 1)) { salsa_set_error("%s: buffer too small", who); return -1; }
+        if (got[t] < 0) { salsa_set_error("%s: a value of edge %zu lies outside [1e-30, 1e30]", who, (size_t)(-got[t] - 1)); return -1; }
+        total += (size_t)got[t];
+    }
+    if (total > out_cap) { salsa_set_error("%s: buffer too small", who); return -1; }
+    th.clear();
+    size_t pos = 0;
+    for (size_t t = 0; t < T; t++) {
+        th.emplace_back([&, t, pos]() { memcpy(out + pos, buf[t].get(), (size_t)got[t]); });
+        pos += (size_t)got[t];
+    }
+    for (auto &x : th) x.join();
+    return (int64_t)total;
+}
+
 // contig_links_iteration_N: "first:X\tsecond:Y\tscore\tcount\n" (make_links.py:169)
 extern "C" int64_t salsa_format_links(const char *names_blob, const int64_t *name_off, const int64_t *first,
                                       const int64_t *second, const uint8_t *ends, const int64_t *count,
                                       const int64_t *digits, const int32_t *exp10, const uint8_t *is_int0, size_t n,
                                       char *out, size_t out_cap)
 {
-    char *p = out;
+    size_t longest = 0;
     for (size_t i = 0; i < n; i++) {
-        int64_t a = first[i], b = second[i];
-        size_t la = (size_t)(name_off[a + 1] - name_off[a]), lb = (size_t)(name_off[b + 1] - name_off[b]);
-        if ((size_t)(p - out) + la + lb + 80 > out_cap) { salsa_set_error("salsa_format_links: buffer too small"); return -1; }
-        memcpy(p, names_blob + name_off[a], la); p += la;
-        *p++ = ':'; *p++ = (ends[i] & 2) ? 'E' : 'B'; *p++ = '\t';
-        memcpy(p, names_blob + name_off[b], lb); p += lb;
-        *p++ = ':'; *p++ = (ends[i] & 1) ? 'E' : 'B'; *p++ = '\t';
-        if (is_int0[i]) *p++ = '0';
-        else {
-            int len = fmt_g12(digits[i], exp10[i], p);
-            if (len < 0) { salsa_set_error("salsa_format_links: score %zu lies outside [1e-30, 1e30]", i); return -1; }
-            p += len;
-        }
-        *p++ = '\t';
-        p = put_i64(p, count[i]);
-        *p++ = '\n';
+        const size_t l = (size_t)(name_off[first[i] + 1] - name_off[first[i]]) + (size_t)(name_off[second[i] + 1] - name_off[second[i]]);
+        if (l > longest) longest = l;
     }
-    return (int64_t)(p - out);
+    auto fmt = [&](size_t lo, size_t hi, char *dst, size_t cap) -> int64_t {
+        char *p = dst;
+        for (size_t i = lo; i < hi; i++) {
+            int64_t a = first[i], b = second[i];
+            size_t la = (size_t)(name_off[a + 1] - name_off[a]), lb = (size_t)(name_off[b + 1] - name_off[b]);
+            if ((size_t)(p - dst) + la + lb + 80 > cap) return -(int64_t)(n + 1);
+            memcpy(p, names_blob + name_off[a], la); p += la;
+            *p++ = ':'; *p++ = (ends[i] & 2) ? 'E' : 'B'; *p++ = '\t';
+            memcpy(p, names_blob + name_off[b], lb); p += lb;
+            *p++ = ':'; *p++ = (ends[i] & 1) ? 'E' : 'B'; *p++ = '\t';
+            if (is_int0[i]) *p++ = '0';
+            else {
+                int len = fmt_g12(digits[i], exp10[i], p);
+                if (len < 0) return -(int64_t)(i + 1);
+                p += len;
+            }
+            *p++ = '\t';
+            p = put_i64(p, count[i]);
+            *p++ = '\n';
+        }
+        return (int64_t)(p - dst);
+    };
+    return format_parallel(n, out, out_cap, longest + 80, fmt, "salsa_format_links");
 }
 
 // contig_links_scaled_iteration_N (fast_scaled_scores.py:86):
@@ -607,23 +663,31 @@ extern "C" int64_t salsa_format_scaled(const char *node_blob, const int64_t *nod
                                        const int32_t *b_exp10, const uint8_t *b_is_int1, const int64_t *r_digits,
                                        const int32_t *r_exp10, const int64_t *links, size_t n, char *out, size_t out_cap)
 {
-    char *p = out;
+    size_t longest = 0;
     for (size_t i = 0; i < n; i++) {
-        int64_t a = u[i], b = v[i];
-        size_t la = (size_t)(node_off[a + 1] - node_off[a]), lb = (size_t)(node_off[b + 1] - node_off[b]);
-        if ((size_t)(p - out) + la + lb + 140 > out_cap) { salsa_set_error("salsa_format_scaled: buffer too small"); return -1; }
-        memcpy(p, node_blob + node_off[a], la); p += la; *p++ = '\t';
-        memcpy(p, node_blob + node_off[b], lb); p += lb; *p++ = '\t';
-        int l1 = fmt_g12(w_digits[i], w_exp10[i], p);
-        if (l1 >= 0) { p += l1; *p++ = '\t'; }
-        int l2 = b_is_int1[i] ? 1 : fmt_g12(b_digits[i], b_exp10[i], p);
-        if (b_is_int1[i]) *p = '1';
-        if (l2 >= 0) { p += l2; *p++ = '\t'; }
-        int l3 = fmt_g12(r_digits[i], r_exp10[i], p);
-        if (l1 < 0 || l2 < 0 || l3 < 0) { salsa_set_error("salsa_format_scaled: a value of edge %zu lies outside [1e-30, 1e30]", i); return -1; }
-        p += l3; *p++ = '\t';
-        p = put_i64(p, links[i]);
-        memcpy(p, "\tFalse\tFalse\n", 13); p += 13;
+        const size_t l = (size_t)(node_off[u[i] + 1] - node_off[u[i]]) + (size_t)(node_off[v[i] + 1] - node_off[v[i]]);
+        if (l > longest) longest = l;
     }
-    return (int64_t)(p - out);
+    auto fmt = [&](size_t lo, size_t hi, char *dst, size_t cap) -> int64_t {
+        char *p = dst;
+        for (size_t i = lo; i < hi; i++) {
+            int64_t a = u[i], b = v[i];
+            size_t la = (size_t)(node_off[a + 1] - node_off[a]), lb = (size_t)(node_off[b + 1] - node_off[b]);
+            if ((size_t)(p - dst) + la + lb + 140 > cap) return -(int64_t)(n + 1);
+            memcpy(p, node_blob + node_off[a], la); p += la; *p++ = '\t';
+            memcpy(p, node_blob + node_off[b], lb); p += lb; *p++ = '\t';
+            int l1 = fmt_g12(w_digits[i], w_exp10[i], p);
+            if (l1 >= 0) { p += l1; *p++ = '\t'; }
+            int l2 = b_is_int1[i] ? 1 : fmt_g12(b_digits[i], b_exp10[i], p);
+            if (b_is_int1[i]) *p = '1';
+            if (l2 >= 0) { p += l2; *p++ = '\t'; }
+            int l3 = fmt_g12(r_digits[i], r_exp10[i], p);
+            if (l1 < 0 || l2 < 0 || l3 < 0) return -(int64_t)(i + 1);
+            p += l3; *p++ = '\t';
+            p = put_i64(p, links[i]);
+            memcpy(p, "\tFalse\tFalse\n", 13); p += 13;
+        }
+        return (int64_t)(p - dst);
+    };
+    return format_parallel(n, out, out_cap, longest + 140, fmt, "salsa_format_scaled");
 }

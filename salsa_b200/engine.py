@@ -305,16 +305,16 @@ class Engine:
         blob, off = _blob(self.names)
         cap = int(sc['n']) * 96 + 2 * int(off[-1] if len(off) else 0) + sum(0 for _ in ()) + 1024
         cap += int((np.diff(off)[sc['first']].sum() + np.diff(off)[sc['second']].sum())) if sc['n'] else 0
-        out = C.create_string_buffer(cap)
+        out = np.empty(cap, dtype=np.uint8)              # (create_string_buffer would zero it, .raw would copy all of it)
         f = np.ascontiguousarray(sc['first'], np.int64); s = np.ascontiguousarray(sc['second'], np.int64)
         e = np.ascontiguousarray(sc['ends'], np.uint8); c = np.ascontiguousarray(sc['count'], np.int64)
         d = np.ascontiguousarray(sc['digits'], np.int64); k = np.ascontiguousarray(sc['exp10'], np.int32)
         z = np.ascontiguousarray(sc['is_int0'], np.uint8)
         nb = self.L.salsa_format_links(blob, off.ctypes.data, f.ctypes.data, s.ctypes.data, e.ctypes.data, c.ctypes.data,
-                                       d.ctypes.data, k.ctypes.data, z.ctypes.data, int(sc['n']), out, cap)
+                                       d.ctypes.data, k.ctypes.data, z.ctypes.data, int(sc['n']), out.ctypes.data, cap)
         if nb < 0:
             check(-2)
-        return out.raw[:nb]
+        return out[:nb].tobytes()
 
     def g12(self, x):
         """(digits, exp10, w12) of Python-2 str(float) for a float64 array (device kernel)."""
