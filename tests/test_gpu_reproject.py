@@ -5,6 +5,7 @@ import os
 import sys
 
 import numpy as np
+import torch
 import pytest
 
 pytestmark = pytest.mark.gpu
@@ -165,6 +166,39 @@ def test_resident_product_feeds_make_links(eng, tmp_path):
     assert t is not None and bytes(t.cpu().numpy()) == got
     open(str(tmp_path / 'got.bed'), 'ab').write(b'X 1 2 q/1\n')          # changed on disk: cache entry must not be used
     assert reproject.resident_bed(str(tmp_path / 'got.bed'), eng.device, load=False) is None
+
+
+def test_stream_in_with_several_readers(eng, tmp_path, monkeypatch):
+    """A file of many chunks is read by several threads side by side (chunks round robin, own pinned buffers and
+    streams): the device copy is the file, whatever the chunk size and the tail."""
+    from salsa_b200 import reproject
+    rng = np.random.default_rng(4)
+    data = rng.integers(0, 256, 5_000_003, dtype=np.uint8).tobytes()
+    p = str(tmp_path / 'big.bin')
+    open(p, 'wb').write(data)
+    for chunk in (1 << 16, 600_000, 1 << 23):
+        monkeypatch.setattr(reproject, 'CHUNK', chunk)
+        t = reproject._stream_in(p, len(data), eng.device)
+        assert bytes(t.cpu().numpy()) == data, chunk
+    open(p, 'wb').write(data[:1000])
+    with pytest.raises(IOError):
+        reproject._stream_in(p, len(data), eng.device)        # the file shrank under the reader
+    assert reproject._stream_in(p, 0, eng.device).numel() == 0
+
+
+def test_after_write_marker_follows_the_file(eng, tmp_path):
+    """A DONE marker requested for a BED that is still being written appears only once the BED is complete on disk."""
+    from salsa_b200 import reproject
+    t = torch.from_numpy(np.random.default_rng(1).integers(0, 256, 3_000_000, dtype=np.uint8)).to(eng.device)
+    dst, marker = str(tmp_path / 'alignment_iteration_9.bed'), str(tmp_path / 'x.DONE')
+    reproject.write_behind(dst, t)
+    reproject.after_write(dst, marker)
+    reproject.flush(dst)
+    assert os.path.exists(marker) and open(dst, 'rb').read() == bytes(t.cpu().numpy())
+    assert os.path.realpath(dst) not in reproject._WRITERS      # the finished writer let go of its slot (and tensor)
+    os.remove(marker)
+    reproject.after_write(dst, marker)                          # nothing in flight: right away
+    assert os.path.exists(marker)
 
 
 def test_write_behind(eng, tmp_path):
