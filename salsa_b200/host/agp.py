@@ -6,23 +6,26 @@ optional second AGP maps `_1`/`_2` pieces back to the pre-cleaning names and coo
 import pickle
 import re
 
-from .clean import read_fasta, wrap_fasta
+from .clean import read_fasta, write_wrapped
 
 _COMP = {'A': 'T', 'B': 'N', 'C': 'G', 'G': 'C', 'T': 'A', 'N': 'N', 'R': 'N', 'M': 'N', 'Y': 'N', 'S': 'N', 'W': 'N', 'K': 'N',
          'V': 'N', 'H': 'N', 'D': 'N', 'a': 't', 'c': 'g', 'g': 'c', 't': 'a', 'n': 'n', ' ': ''}
 
 
-_TABLE = str.maketrans(_COMP)
-
-
 _KNOWN = ''.join(_COMP.keys()).encode('latin-1')
+_TABLE = bytes.maketrans(''.join(k for k, v in _COMP.items() if v).encode('latin-1'), ''.join(v for v in _COMP.values() if v).encode('latin-1'))
+_DROP = ''.join(k for k, v in _COMP.items() if not v).encode('latin-1')       # ' ' maps to nothing
 
 
 def revcomp(s):
-    bad = s.encode('latin-1', 'replace').translate(None, _KNOWN)       # what is left is outside the table
+    """Reverse complement by the reference's table (get_seq.py:8-16) of a sequence given as latin-1 bytes (or str:
+    returned as str).  A character outside the table raises KeyError, as the reference's dict lookup does."""
+    b = s if isinstance(s, (bytes, bytearray)) else s.encode('latin-1', 'replace')
+    bad = b.translate(None, _KNOWN)                                    # what is left is outside the table
     if bad:
-        raise KeyError(min(set(s) - _COMP.keys()))                     # the reference's table lookup raises on other characters
-    return s.translate(_TABLE)[::-1]
+        raise KeyError(min(set(s) - _COMP.keys()) if isinstance(s, str) else chr(min(bad)))
+    r = b.translate(_TABLE, _DROP)[::-1]
+    return r if isinstance(s, (bytes, bytearray)) else r.decode('latin-1')
 
 
 def original_coords(name, position, breaks):
@@ -46,7 +49,7 @@ def write_outputs(cleaned, scaffold_map_path, fasta_out, agp_out, breaks_path=No
                 t = line.rstrip('\n').split('\t')
                 assert t[0] not in breaks
                 breaks[t[0]] = int(t[1])
-    seq = read_fasta(cleaned)
+    seq = read_fasta(cleaned, as_bytes=True)
     clen = {k: len(v) for k, v in seq.items()}
     total = {s: sum(clen[p[i].split(':')[0]] for i in range(0, len(p) - 1, 2)) for s, p in scaff_map.items()}
     ranked = sorted(total.items(), key=lambda kv: kv[1], reverse=True)        # stable: ties keep map order
@@ -74,7 +77,7 @@ def write_outputs(cleaned, scaffold_map_path, fasta_out, agp_out, breaks_path=No
                     orig.write('\t'.join(cols))
                 start, comp = end + 1, comp + 1
                 if i != len(path) - 2:
-                    parts.append('N' * 100)
+                    parts.append(b'N' * 100)
                     end = 100 + start - 1
                     gap = 'scaffold_%d\t%d\t%d\t%d\tU\t100\tscaffold\tyes\tproximity_ligation\n' % (cid, start, end, comp)
                     agp.write(gap)
@@ -82,6 +85,6 @@ def write_outputs(cleaned, scaffold_map_path, fasta_out, agp_out, breaks_path=No
                         orig.write(gap)
                     start, comp = end + 1, comp + 1
             fa.write(b'>scaffold_%d\n' % cid)
-            fa.write(wrap_fasta(''.join(parts)))
+            write_wrapped(fa, b''.join(parts))
     if orig:
         orig.close()

@@ -22,8 +22,8 @@ def _read_fasta_lines(path):
     return {k: ''.join(v) for k, v in fa.items()}
 
 
-def read_fasta(path):
-    """name -> sequence (lines rstripped and joined), later duplicate wins (correct.py:4-19).
+def read_fasta(path, as_bytes=False):
+    """name -> sequence (lines rstripped and joined; latin-1 bytes when as_bytes), later duplicate wins (correct.py:4-19).
     Whole records at a time (a 3 Gb assembly has 50 million lines); anything unusual -- text before the first
     header, whitespace other than the newlines inside a record -- goes through the line loop, which is the
     reference's own and raises what it raises."""
@@ -31,8 +31,9 @@ def read_fasta(path):
         data = fh.read()
     if not data:
         return {}
+    slow = (lambda: {k: v.encode('latin-1') for k, v in _read_fasta_lines(path).items()}) if as_bytes else (lambda: _read_fasta_lines(path))
     if data[:1] != b'>':
-        return _read_fasta_lines(path)
+        return slow()
     starts, q = [0], data.find(b'\n>')
     while q >= 0:
         starts.append(q + 1)
@@ -44,8 +45,9 @@ def read_fasta(path):
         head = data[b + 1:nl if nl >= 0 else e]
         body = data[nl + 1:e] if nl >= 0 else b''
         if not head.split() or any(c in body for c in (b' ', b'\t', b'\r', b'\x0b', b'\x0c')) or b'\r' in head:
-            return _read_fasta_lines(path)
-        fa[head.decode('latin-1').rstrip().split()[0]] = _unwrap(body).decode('latin-1')
+            return slow()
+        seq = _unwrap(body)
+        fa[head.decode('latin-1').rstrip().split()[0]] = seq if as_bytes else seq.decode('latin-1')
     return fa
 
 
@@ -66,22 +68,36 @@ def _unwrap(body):
     return a[:, :w].copy().tobytes() + tail.rstrip(b"\n")
 
 
-def wrap_fasta(s, width=80):
-    """The sequence in lines of `width` characters, every line (the last, shorter one too) ending in a newline: what
-    `for i in range(0, len(s), width): write(s[i:i + width] + '\\n')` writes, as one bytes object."""
-    b = s.encode('latin-1')
+def _wrapped(s, width):
+    b = s if isinstance(s, (bytes, bytearray)) else s.encode('latin-1')
     k = len(b) // width
     out = np.empty((k, width + 1), np.uint8)
     out[:, :width] = np.frombuffer(b, dtype=np.uint8, count=k * width).reshape(k, width)
     out[:, width] = 10
     tail = b[k * width:]
-    return out.tobytes() + (tail + b'\n' if tail else b'')
+    return out, (tail + b'\n' if tail else b'')
+
+
+def wrap_fasta(s, width=80):
+    """The sequence (str or latin-1 bytes) in lines of `width` characters, every line (the last, shorter one too) ending
+    in a newline: what `for i in range(0, len(s), width): write(s[i:i + width] + '\\n')` writes, as one bytes object."""
+    out, tail = _wrapped(s, width)
+    return out.tobytes() + tail
+
+
+def write_wrapped(fh, s, width=80):
+    """fh.write(wrap_fasta(s)) without the intermediate copy (fh: binary file)."""
+    out, tail = _wrapped(s, width)
+    if out.size:
+        fh.write(out)
+    if tail:
+        fh.write(tail)
 
 
 def clean(assembly, breaks_path, bed, outdir, flush_every=1000000, bed_pass=None):
     """bed_pass(src, dst, names, cut, flush_every) does the BED rewrite: the step script passes the CUDA one
     (salsa_b200.reproject.clean_pass); without it the line loop below runs (the tests' CPU path)."""
-    seqs = read_fasta(assembly)
+    seqs = read_fasta(assembly, as_bytes=True)
     cut = {}
     with open(breaks_path, 'r', encoding='latin-1') as f:
         for line in f:
@@ -101,7 +117,7 @@ def clean(assembly, breaks_path, bed, outdir, flush_every=1000000, bed_pass=None
     with open(outdir + '/asm.cleaned.fasta', 'wb') as fo:
         for name, s in new_seq.items():
             fo.write(('>' + name + '\n').encode('latin-1'))
-            fo.write(wrap_fasta(s))
+            write_wrapped(fo, s)
     with open(outdir + '/scaffold_length_iteration_1', 'w') as fo:
         for name, s in new_seq.items():
             fo.write('%s\t%d\n' % (name, len(s)))

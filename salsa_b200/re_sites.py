@@ -44,14 +44,15 @@ class _DeviceView:
         return self.t[key].cpu().numpy()
 
 
-def count_sites(eng, fasta, enzyme, timers=None):
+def count_sites(eng, fasta, enzyme, timers=None, device_copy=None):
     """fasta: host uint8 numpy array (np.memmap works) or a uint8 CUDA tensor.  Returns
     (names, left, right, seqlen) in first-appearance order of record names; a repeated
     name keeps its first position and its last sequence (dict assignment, RE_sites.py:19).
-    timers: optional dict that receives (start, end) CUDA event pairs per stage."""
+    timers: optional dict that receives (start, end) CUDA event pairs per stage.
+    device_copy: the same bytes already on the device (the header lines are still read from `fasta` on the host)."""
     L, dev = eng.L, eng.device
     st = torch.cuda.current_stream().cuda_stream
-    d = None
+    d = device_copy
     if isinstance(fasta, torch.Tensor):
         d = fasta
         fasta = _DeviceView(d)
