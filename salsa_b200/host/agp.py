@@ -13,7 +13,8 @@ _COMP = {'A': 'T', 'B': 'N', 'C': 'G', 'G': 'C', 'T': 'A', 'N': 'N', 'R': 'N', '
 
 
 _KNOWN = ''.join(_COMP.keys()).encode('latin-1')
-_TABLE = bytes.maketrans(''.join(k for k, v in _COMP.items() if v).encode('latin-1'), ''.join(v for v in _COMP.values() if v).encode('latin-1'))
+# complement table over all 256 byte values: anything outside the reference's table becomes NUL (itself outside it)
+_TABLE = bytes(ord(COMP_) if COMP_ else 0 for COMP_ in (_COMP.get(chr(i), '') for i in range(256)))
 _DROP = ''.join(k for k, v in _COMP.items() if not v).encode('latin-1')       # ' ' maps to nothing
 
 
@@ -21,10 +22,11 @@ def revcomp(s):
     """Reverse complement by the reference's table (get_seq.py:8-16) of a sequence given as latin-1 bytes (or str:
     returned as str).  A character outside the table raises KeyError, as the reference's dict lookup does."""
     b = s if isinstance(s, (bytes, bytearray)) else s.encode('latin-1', 'replace')
-    bad = b.translate(None, _KNOWN)                                    # what is left is outside the table
-    if bad:
+    r = b.translate(_TABLE, _DROP)
+    if b'\0' in r:
+        bad = b.translate(None, _KNOWN)                                # what is left is outside the table
         raise KeyError(min(set(s) - _COMP.keys()) if isinstance(s, str) else chr(min(bad)))
-    r = b.translate(_TABLE, _DROP)[::-1]
+    r = r[::-1]
     return r if isinstance(s, (bytes, bytearray)) else r.decode('latin-1')
 
 

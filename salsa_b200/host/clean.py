@@ -60,10 +60,10 @@ def _unwrap(body):
     k = len(body) // (w + 1)
     tail = body[k * (w + 1):]
     tn = tail.count(b'\n')
-    if tn > 1 or (tn == 1 and tail[-1:] != b'\n') or body.count(b'\n') != k + tn:
+    if tn > 1 or (tn == 1 and tail[-1:] != b'\n'):
         return body.translate(None, b'\n')
     a = np.frombuffer(body, dtype=np.uint8, count=k * (w + 1)).reshape(k, w + 1)
-    if not (a[:, w] == 10).all():
+    if np.count_nonzero(a == 10) != k or not (a[:, w] == 10).all():       # exactly one newline per row, at its end
         return body.translate(None, b'\n')
     return a[:, :w].copy().tobytes() + tail.rstrip(b"\n")
 
