@@ -36,10 +36,16 @@ using namespace bedscan;
 constexpr int RING = SALSA_STREAM_RING;     // bytes of text a warp keeps in shared memory
 constexpr int GRP = 2048;                   // bytes per cp.async group = one classification iteration (64 bytes per lane)
 constexpr int NGR = RING / GRP;
-constexpr int MIRROR = 256;                 // the ring's first bytes repeated behind its end: reads never wrap
+#ifndef SALSA_STREAM_MIRROR
+#define SALSA_STREAM_MIRROR 256
+#endif
+#ifndef SALSA_STREAM_LCAP
+#define SALSA_STREAM_LCAP 256
+#endif
+constexpr int MIRROR = SALSA_STREAM_MIRROR;  // the ring's first bytes repeated behind its end: reads never wrap (>= 128: phase 1 reads 96 bitmap bits and ~72 bytes from a line's start)
 constexpr int FRONT = 16;                   // addressable bytes before the ring (masked-off window bytes)
 constexpr int OVER = 160;                   // phase 1 looks at a line once this much behind its start is classified
-constexpr int LCAP = 256;                   // ring of line starts (entries)
+constexpr int LCAP = SALSA_STREAM_LCAP;      // ring of line starts (entries; >= 128: an iteration adds up to 64 without asking)
 constexpr int QCAP = 64;                    // ring of queued pairs (entries of 16 bytes)
 constexpr int QPAIRS = 16;                  // pairs per phase-2 batch (two lanes each)
 constexpr int WARPS = SALSA_STREAM_WARPS;   // warps per CTA (they share nothing but the mask table)
