@@ -531,10 +531,27 @@ __device__ Rec parse_global_line(const ScanArgs &A, const Smem &S, long long st,
 }
 
 // Thread 0: was entry 0 (the line before the first owned line) skipped, and if so which
-// earlier line is the effective "previous" of the first owned line?  Walks back through global
-// memory to the nearest line that is certainly kept (its contig is in no avoid pair, or it is the
-// buffer's first line) -- however far that is -- and replays the reference's loop forward from there
-// (make_links.py:72-74: a skipped line does not become prev_line).
+// earlier line is the effective "previous" of the first owned line?  (make_links.py:72-74: a skipped
+// line does not become prev_line.)
+//
+// The answer depends on the contig of prev_line when the loop reaches entry 0.  It is known for certain
+// behind a line whose contig is in no avoid pair (or the buffer's first line): round 2's first version
+// walked back to the nearest such anchor however far that was -- a walk to the start of the file, for
+// every tile, once every contig is in some avoid pair (a late iteration with a few dozen scaffolds).
+// Now the walk goes back W lines (16, then x4 while the answer stays open) and replays forward with the
+// SET of states prev_line can be in: before the window's first line it is unknown; behind it it is that
+// line (kept) or one of the few contigs that line is avoid-paired with (skipped: an older line we have
+// not seen); every further line either keeps a state (pair avoided) or replaces it by itself, so the set
+// shrinks to one state within a few lines unless the text alternates between the two contigs of one
+// avoid pair.  The answer is taken only when every state left gives the same one; a window that reaches
+// an anchor or the start of the buffer is exact by construction, so the result never depends on W.
+struct AvState {
+    int id;                   // contig of prev_line
+    long long st;             // abase coordinate of that line, -1: a line before the window (position unknown)
+    int len;
+};
+constexpr int AV_STATES = 8;
+
 template <class Policy>
 __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
 {
@@ -544,33 +561,75 @@ __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
     const long long g0 = sb + (long long)S.lines[0];
     const long long mis = (long long)A.mis;
     if (!idv_inv(v0) || g0 <= mis) return;            // certainly kept (or the buffer's first line: always "previous")
-    long long cur = g0, prev_st = 0;
-    int prev_len = 0, prev_id = -1;
-    for (;;) {                                        // back to the anchor
-        long long e = cur - 1;                        // the '\n' that ends the previous line
-        long long st = e;
-        while (st > mis && A.abase[st - 1] != '\n' && e - st <= SALSA_MAX_LINE) st--;
-        if (e - st > SALSA_MAX_LINE) {
-            report(A.stats, A.base_offset + (uint64_t)(st - mis), SALSA_DATA_LINE_TOO_LONG);
-            return;
+    for (long long W = 16;; W *= 4) {
+        // ---- back: W lines, or to an anchor ----
+        long long cur = g0, first_st = g0;
+        bool anchored = false;
+        for (long long k = 0; k < W; k++) {
+            long long e = cur - 1;                    // the '\n' that ends the previous line
+            long long st = e;
+            while (st > mis && A.abase[st - 1] != '\n' && e - st <= SALSA_MAX_LINE) st--;
+            if (e - st > SALSA_MAX_LINE) {
+                report(A.stats, A.base_offset + (uint64_t)(st - mis), SALSA_DATA_LINE_TOO_LONG);
+                return;
+            }
+            first_st = st;
+            Rec r = parse_global_line<Policy>(A, S, st, (int)(e - st));
+            bool inv = r.id >= 0 && (A.t.meta[r.id].flags & CTG_INVOLVED);
+            if (!inv || st <= mis) { anchored = true; break; }
+            cur = st;
         }
-        Rec r = parse_global_line<Policy>(A, S, st, (int)(e - st));
-        bool inv = r.id >= 0 && (A.t.meta[r.id].flags & CTG_INVOLVED);
-        if (!inv || st <= mis) { prev_st = st; prev_len = (int)(e - st); prev_id = r.id; break; }
-        cur = st;
-    }
-    long long pos = prev_st + prev_len + 1;           // forward again: every line between the anchor and entry 0
-    while (pos < g0) {
-        long long en = pos;
-        while (en < g0 - 1 && A.abase[en] != '\n') en++;
-        Rec r = parse_global_line<Policy>(A, S, pos, (int)(en - pos));     // (its length was checked on the way back)
-        if (!avoid_has(A.t, prev_id, r.id)) { prev_st = pos; prev_len = (int)(en - pos); prev_id = r.id; }
-        pos = en + 1;
-    }
-    if (avoid_has(A.t, prev_id, idv_id(v0))) {
-        *S.ext = parse_global_line<Policy>(A, S, prev_st, prev_len);       // stays in the spare buffer for byte compares
-        S.extinfo[0] = 1;
-        S.extinfo[1] = prev_id;
+        // ---- forward: the states prev_line can be in ----
+        AvState set[AV_STATES];
+        int ns = 0;
+        bool open_ = false;                           // true: the window cannot settle the question
+        long long pos = first_st;
+        bool first = true;
+        while (pos < g0 && !open_) {
+            long long en = pos;
+            while (en < g0 - 1 && A.abase[en] != '\n') en++;
+            Rec r = parse_global_line<Policy>(A, S, pos, (int)(en - pos));     // (its length was checked on the way back)
+            if (first) {
+                first = false;
+                set[ns++] = AvState{r.id, pos, (int)(en - pos)};             // the line itself: kept
+                if (!anchored && r.id >= 0) {
+                    // ... or skipped, behind an unseen line on a contig it is avoid-paired with
+                    const unsigned long long k0 = (unsigned long long)(uint32_t)r.id << 32;
+                    int lo = 0, hi = A.t.navoid;
+                    while (lo < hi) {
+                        int mid = (lo + hi) >> 1;
+                        if (A.t.avoid[mid] < k0) lo = mid + 1; else hi = mid;
+                    }
+                    for (; lo < A.t.navoid && (A.t.avoid[lo] >> 32) == (unsigned long long)(uint32_t)r.id; lo++) {
+                        if (ns == AV_STATES) { open_ = true; break; }
+                        set[ns++] = AvState{(int)(uint32_t)A.t.avoid[lo], -1, 0};
+                    }
+                }
+            } else {
+                int m = 0;
+                bool replaced = false;
+                for (int q = 0; q < ns; q++) {
+                    if (avoid_has(A.t, set[q].id, r.id)) set[m++] = set[q];   // pair avoided: prev_line stays
+                    else replaced = true;
+                }
+                if (replaced) set[m++] = AvState{r.id, pos, (int)(en - pos)};
+                ns = m;
+            }
+            pos = en + 1;
+        }
+        if (!open_) {
+            // entry 0 against every state that is left
+            int nskip = 0;
+            for (int q = 0; q < ns; q++) nskip += avoid_has(A.t, set[q].id, idv_id(v0)) ? 1 : 0;
+            if (nskip == 0) return;                   // kept, whatever came before
+            if (nskip == ns && ns == 1 && set[0].st >= 0) {
+                *S.ext = parse_global_line<Policy>(A, S, set[0].st, set[0].len);   // stays in the spare buffer for byte compares
+                S.extinfo[0] = 1;
+                S.extinfo[1] = set[0].id;
+                return;
+            }
+        }
+        // undecided: look further back (an anchored window is always decided: one state, position known)
     }
 }
 

@@ -185,6 +185,48 @@ def bench_cov(eng, asm, dev, pairs):
     del buf, diff
 
 
+def bench_avoid(eng, asm, dev, pairs):
+    """make_links.py of an iteration >= 2: the same scan with links_avoid_iteration_N loaded (the tile scanner with the
+    walk-back / replay of bed_scan.cuh).  Three avoid lists: a handful of scaffold pairs (what refactor_breaks.py writes),
+    10 % of the contigs involved, every contig involved (the worst case: no line is certainly kept)."""
+    n = asm.ncontig
+    one = np.ones(n, np.int64)
+    buf = torch.empty(int(pairs * 2.02 * 47) + (1 << 20), dtype=torch.uint8, device=dev)
+    pos, done = 0, 0
+    while done < pairs:
+        m = min(20_000_000, pairs - done)
+        rec = synth.gen_records(asm, m, seed=700 + done, device=dev, read_id_base=done)
+        out = synth.format_bed(rec, out=buf[pos:])
+        pos += out.numel()
+        done += m
+        del rec, out
+    bed = buf[:pos]
+    rng = np.random.default_rng(11)
+    counted = {}
+    for label, k in (('no avoid list (streaming scanner)', 0), ('30 avoid pairs', 30), ('avoid pairs over 10 % of the contigs', n // 20),
+                     ('every contig in an avoid pair', n)):
+        if k == 0:
+            avoid = []
+        elif k == n:
+            perm = rng.permutation(n)
+            avoid = [(asm.names[perm[i]], asm.names[perm[(i + 1) % n]]) for i in range(n)]
+        else:
+            idx = rng.choice(n, size=2 * k, replace=False)
+            avoid = [(asm.names[idx[2 * i]], asm.names[idx[2 * i + 1]]) for i in range(k)]
+        eng.set_contigs(asm.names, asm.lengths, re_left=one, re_right=one, avoid=avoid)
+        eng.begin_links('dense')
+
+        def run():
+            eng.ingest_device(bed)
+        ms = timed(run)
+        st = eng.stats_read()
+        counted[label] = int(st.pairs)
+        emit('bed_ingest, %s' % label, ms, bed.numel(), pairs=pairs, avoid_pairs=len(avoid),
+             counted_pairs_total=int(st.pairs), note='dense table; BED text read once')
+    eng.set_contigs(asm.names, asm.lengths)
+    del buf, bed
+
+
 def bench_score(eng, dev, n=3000, E=18_000_000):
     rng = np.random.default_rng(1)
     a = rng.integers(0, n, E * 2)
@@ -240,6 +282,9 @@ def main():
         torch.cuda.empty_cache()
     if args.only in ('', 'cov'):
         bench_cov(eng, asm, dev, 10_000_000 if args.quick else 100_000_000)
+        torch.cuda.empty_cache()
+    if args.only in ('', 'avoid'):
+        bench_avoid(eng, asm, dev, 10_000_000 if args.quick else 100_000_000)
         torch.cuda.empty_cache()
     if args.only in ('', 'score'):
         bench_score(eng, dev, E=2_000_000 if args.quick else 18_000_000)
