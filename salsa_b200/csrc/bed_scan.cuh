@@ -908,18 +908,6 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     // ---- parse + pair ---------------------------------------------------
     const int K = n + 1;
     const int first_line_idx = (int)((long long)A.mis - sb);     // smem index of the buffer's first line (tile 0 only)
-    if (Policy::AVOID) {
-        // pass A: contig id (+ "in some avoid pair") of every line; thread 0 settles what happened before the tile
-        for (int e = tid; e < K; e += NTHREADS) {
-            Rec r = parse_any<Policy>(A, S, S.lines[e], sent, trunc, true);
-            int v = r.id;
-            if (v >= 0 && (A.t.meta[v].flags & CTG_INVOLVED)) v |= IDV_INVOLVED;
-            S.idv[e] = v;
-        }
-        __syncthreads();
-        if (tid == 0) resolve_entry0<Policy>(A, S, sb);
-        __syncthreads();
-    }
     for (int r0 = 0; r0 < K; r0 += NTHREADS) {
         int e = r0 + tid;
         Rec rec;
@@ -930,9 +918,20 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
         if (e < K) {
             lstart = S.lines[e];
             rec = parse_any<Policy>(A, S, lstart, sent, trunc, true);
+            if (Policy::AVOID) {
+                // contig id (+ "in some avoid pair") of every line, for the chain logic below: lines of earlier rounds and of
+                // this one are all there behind the barrier
+                int v = rec.id;
+                if (v >= 0 && (A.t.meta[v].flags & CTG_INVOLVED)) v |= IDV_INVOLVED;
+                S.idv[e] = v;
+            }
         }
         if (lane == 31) S.carry[warp + 1] = rec;
         __syncthreads();
+        if (Policy::AVOID && r0 == 0) {
+            if (tid == 0) resolve_entry0<Policy>(A, S, sb);      // thread 0 settles what happened before the tile
+            __syncthreads();
+        }
         Rec pv = rec_shfl_up(rec);
         int pstart = __shfl_up_sync(0xffffffffu, lstart, 1);
         if (lane == 0) { pv = S.carry[warp]; pstart = -2; }
