@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(CT) chunk_sum_kernel(const int *diff, const Se
 
 // cexcl: exclusive scan of csum over ALL chunks (two's complement), so the prefix
 // inside a segment is cexcl[g] - cexcl[first chunk of the segment]
-__global__ void __launch_bounds__(CT) chunk_scan_kernel(const int *diff, int *cov, const Seg *segs, const uint64_t *seg_chunk_off,
+__global__ void __launch_bounds__(CT, 8) chunk_scan_kernel(const int *diff, int *cov, const Seg *segs, const uint64_t *seg_chunk_off,
                                                         int nseg, const unsigned long long *cexcl, unsigned long long *seg_sum)
 {
     __shared__ unsigned wsum[CT / 32];
