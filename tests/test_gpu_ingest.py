@@ -176,6 +176,27 @@ def test_sparse_table_grows_like_the_reference_dict(eng, oracle_lib):
     assert got == want and sum(got.values()) == st.pairs
 
 
+def test_100k_contigs_sparse_against_the_oracle(eng, oracle_lib):
+    """BASELINE configs[4]'s contig count (dense table impossible: 'auto' must pick the sparse one), 1.5 M pairs:
+    the link list equals the oracle's."""
+    from salsa_b200 import synth
+    asm = synth.make_assembly(ncontig=100_000, genome=300_000_000, len_lo=1_000, len_hi=20_000, nchrom=23, seed=4)
+    rec = synth.gen_records(asm, 1_500_000, seed=8, noise=0.05, triple=0.002)
+    bed = bytes(synth.format_bed(rec).numpy())
+    n = asm.ncontig
+    one = np.ones(n, np.int64)
+    want = oracle_lib.make_links(bed, asm.names, asm.lengths.astype(float), np.ones(n, np.uint8), one, one)
+    eng.set_contigs(asm.names, asm.lengths.astype(np.int64), one, one)
+    dev = torch.frombuffer(bytearray(bed), dtype=torch.uint8).to(eng.device)
+    st = eng.ingest_links(lambda: eng.ingest_device(dev))
+    assert eng.mode == 'sparse'
+    f, s2, e, c = eng.links()
+    got = {(eng.names[a], eng.names[b], int(x)): int(y) for a, b, x, y in zip(f, s2, e, c)}
+    exp = {(asm.names[a], asm.names[b], int(x)): int(y) for a, b, x, y in zip(want['first'], want['second'], want['ends'], want['count'])}
+    assert st.pairs == int(want['npairs_counted']) and len(exp) > 100_000
+    assert got == exp
+
+
 def test_timers_through_the_abi(eng):
     from salsa_b200 import synth
     asm, rec, bed = synth.small_case(ncontig=30, genome=600_000, npairs=20000, seed=5)

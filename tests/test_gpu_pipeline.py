@@ -53,6 +53,19 @@ def test_spawned_steps_equal_in_process_steps(tmp_path):
     assert not [f for f in os.listdir(str(tmp_path / 'inproc')) if f.endswith('.part')]
 
 
+def test_dnase_with_misassembly_correction(tmp_path, oracle_lib):
+    """BASELINE configs[2] shape, scaled down: -e DNASE (RE counts = len / 2, RE_sites.py:39-43) with -m yes on a genome
+    whose contigs are long enough for both coverage programs to do real work, 3 iterations."""
+    data = str(tmp_path / 'data')
+    pu.write_dataset(data, ncontig=40, genome=60_000_000, len_lo=400_000, len_hi=3_500_000, npairs=2_000_000, seed=77, nchrom=3)
+    obin = pu.make_oracle_bin(str(tmp_path / 'obin'))
+    args = ['-e', 'DNASE', '-i', '3', '-m', 'yes']
+    run(pu.BIN, data, str(tmp_path / 'gpu'), args)
+    run(obin, data, str(tmp_path / 'ora'), args)
+    g = compare(str(tmp_path / 'gpu'), str(tmp_path / 'ora'))
+    assert 'input_breaks' in g and 'misasm_iteration_2.report' in g and 'scaffolds_FINAL.fasta' in g
+
+
 def test_misassembly_and_gfa(tmp_path, oracle_lib):
     """>= 1 Mb contigs so break_contigs_start / break_contigs do real work; -m yes, -g GFA, Arima enzymes."""
     data = str(tmp_path / 'data')
