@@ -199,6 +199,17 @@ class Engine:
         size = os.path.getsize(path)
         if size == 0:
             return
+        if self.navoid:
+            # With an avoid list a chunk may only start on a line that can never be skipped (make_links.py:72-74); a BED
+            # whose every scaffold is in some avoid pair has no such line.  A BED that fits the GPU therefore goes there in
+            # one piece (the kernel resolves chains of any length), and only a larger one is cut.
+            free, _ = torch.cuda.mem_get_info(self.device)
+            if size + (256 << 20) < free:
+                from .reproject import _stream_in
+                dev = _stream_in(os.path.realpath(path), size, self.device)
+                self.ingest_device(dev)
+                torch.cuda.current_stream().synchronize()
+                return
         mm = np.memmap(path, dtype=np.uint8, mode='r')
         if self.mode == 'dense':
             self.ingest_host(mm, chunk_bytes=min(chunk_bytes, 64 << 20))

@@ -117,6 +117,27 @@ def test_long_avoid_chains_across_tiles(eng, oracle_lib):
         assert gpu_dict(eng, bed, names, L, avoid) == oracle_dict(oracle_lib, bed, names, L, avoid)
 
 
+def test_file_ingest_when_every_contig_is_avoid_listed(eng, oracle_lib, tmp_path):
+    """Engine.ingest_file (what make_links.py -b does): with every scaffold in some avoid pair no line is certainly kept,
+    so the file cannot be cut into chunks -- a BED that fits the GPU goes there in one piece and the result is the
+    reference's (the step may be slower on such an input, it may not fail)."""
+    names, L = [b'a', b'b', b'c', b'd'], [100] * 4
+    avoid = [(b'a', b'b'), (b'b', b'c'), (b'a', b'c'), (b'a', b'd'), (b'b', b'd'), (b'c', b'd')]
+    rng = np.random.default_rng(16)
+    lines = [names[int(rng.integers(0, 4))] + b' %d %d r%d/%d' % (1 + i % 90, 2 + i % 90, i // 2, 1 + i % 2) for i in range(20000)]
+    bed = b'\n'.join(lines) + b'\n'
+    p = str(tmp_path / 'all_involved.bed')
+    open(p, 'wb').write(bed)
+    n = len(names)
+    for mode in ('dense', 'sparse'):
+        eng.set_contigs(names, np.asarray(L, np.int64), np.ones(n, np.int64), np.ones(n, np.int64), None, avoid)
+        eng.begin_links(mode, sparse_capacity=1 << 12)
+        eng.ingest_file(p, chunk_bytes=1 << 16)
+        eng.stats_read()
+        f, s, e, c = eng.links()
+        assert {(eng.names[a], eng.names[b], int(x)): int(y) for a, b, x, y in zip(f, s, e, c)} == oracle_dict(oracle_lib, bed, names, L, avoid)
+
+
 def test_host_streaming_with_avoid_list(eng, oracle_lib):
     """salsa_bed_ingest_dense_host with an avoid set: chunks are cut at lines that can never be skipped."""
     from salsa_b200 import synth
