@@ -91,7 +91,10 @@ struct Smem {
 };
 
 constexpr int IDV_INVOLVED = 0x40000000;
-__device__ __forceinline__ int idv_id(int v) { return v < 0 ? -1 : (v & 0x3FFFFFFF); }
+constexpr int IDV_KEPT = 0x20000000;       // the line is not skipped by the avoid rule (current iterate of the fixed point below)
+constexpr int IDV_NEXT = 0x10000000;       // ... its next iterate
+__device__ __forceinline__ int idv_id(int v) { return v < 0 ? -1 : (v & 0x0FFFFFFF); }
+__device__ __forceinline__ bool idv_kept(int v) { return v < 0 || (v & IDV_KEPT); }
 __device__ __forceinline__ bool idv_inv(int v) { return v >= 0 && (v & IDV_INVOLVED); }
 
 __device__ __forceinline__ long long rec_start(const Rec &r)
@@ -538,7 +541,7 @@ __device__ Rec parse_global_line(const ScanArgs &A, const Smem &S, long long st,
 // behind a line whose contig is in no avoid pair (or the buffer's first line): round 2's first version
 // walked back to the nearest such anchor however far that was -- a walk to the start of the file, for
 // every tile, once every contig is in some avoid pair (a late iteration with a few dozen scaffolds).
-// Now the walk goes back W lines (16, then x4 while the answer stays open) and replays forward with the
+// Now the walk goes back W lines (4, then x4 while the answer stays open) and replays forward with the
 // SET of states prev_line can be in: before the window's first line it is unknown; behind it it is that
 // line (kept) or one of the few contigs that line is avoid-paired with (skipped: an older line we have
 // not seen); every further line either keeps a state (pair avoided) or replaces it by itself, so the set
@@ -561,7 +564,7 @@ __device__ void resolve_entry0(const ScanArgs &A, const Smem &S, long long sb)
     const long long g0 = sb + (long long)S.lines[0];
     const long long mis = (long long)A.mis;
     if (!idv_inv(v0) || g0 <= mis) return;            // certainly kept (or the buffer's first line: always "previous")
-    for (long long W = 16;; W *= 4) {
+    for (long long W = 4;; W *= 4) {
         // ---- back: W lines, or to an anchor ----
         long long cur = g0, first_st = g0;
         bool anchored = false;
@@ -908,6 +911,49 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
     // ---- parse + pair ---------------------------------------------------
     const int K = n + 1;
     const int first_line_idx = (int)((long long)A.mis - sb);     // smem index of the buffer's first line (tile 0 only)
+    bool av_fixed = false;       // avoid mode: the kept flags in S.idv are final (else: per-line replay below)
+    if (Policy::AVOID) {
+        // contig id (+ "in some avoid pair") of every line; thread 0 settles what happened before the tile
+        for (int e = tid; e < K; e += NTHREADS) {
+            Rec r = parse_any<Policy>(A, S, S.lines[e], sent, trunc, true);
+            int v = r.id;
+            if (v >= 0) v |= IDV_KEPT | ((A.t.meta[v].flags & CTG_INVOLVED) ? IDV_INVOLVED : 0);
+            S.idv[e] = v;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            resolve_entry0<Policy>(A, S, sb);
+            if (S.extinfo[0] && S.idv[0] >= 0) S.idv[0] &= ~IDV_KEPT;
+        }
+        __syncthreads();
+        // Which lines does the reference skip?  Line e is skipped iff its contig is avoid-paired with the contig of the
+        // nearest line before it that was NOT skipped -- a left-to-right recurrence.  Its solution is the only fixed point
+        // of "skipped(e) computed from the current guess of the lines before e", and iterating from "nothing is skipped"
+        // gets every line right whose chain of skipped predecessors is shorter than the number of rounds: a handful in
+        // any real BED.  Each round is O(1) per line, where replaying the chain from its start for every line
+        // (round 1; kept below for texts that do not settle in 48 rounds) is quadratic in the length of a run of
+        // avoid-listed lines -- 0.5 s per 10 GB once every scaffold is in some avoid pair.
+        for (int round = 0; round < 48 && !av_fixed; round++) {
+            int changed = 0;
+            for (int e = 1 + tid; e < K; e += NTHREADS) {
+                int v = S.idv[e];
+                if (!idv_inv(v)) continue;                               // never skipped
+                int j = e - 1;
+                while (j > 0 && !idv_kept(S.idv[j])) j--;
+                const int pid = (j == 0 && !idv_kept(S.idv[0])) ? S.extinfo[1] : idv_id(S.idv[j]);
+                const bool kept = !avoid_has(A.t, pid, idv_id(v));
+                changed |= (kept != ((v & IDV_KEPT) != 0));
+                S.idv[e] = kept ? (v | IDV_NEXT) : (v & ~IDV_NEXT);      // (only this thread writes entry e; bit KEPT is untouched)
+            }
+            changed = __syncthreads_or(changed);
+            for (int e = 1 + tid; e < K; e += NTHREADS) {
+                int v = S.idv[e];
+                if (idv_inv(v)) S.idv[e] = (v & IDV_NEXT) ? (v | IDV_KEPT) : (v & ~IDV_KEPT);
+            }
+            __syncthreads();
+            av_fixed = changed == 0;
+        }
+    }
     for (int r0 = 0; r0 < K; r0 += NTHREADS) {
         int e = r0 + tid;
         Rec rec;
@@ -918,20 +964,9 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
         if (e < K) {
             lstart = S.lines[e];
             rec = parse_any<Policy>(A, S, lstart, sent, trunc, true);
-            if (Policy::AVOID) {
-                // contig id (+ "in some avoid pair") of every line, for the chain logic below: lines of earlier rounds and of
-                // this one are all there behind the barrier
-                int v = rec.id;
-                if (v >= 0 && (A.t.meta[v].flags & CTG_INVOLVED)) v |= IDV_INVOLVED;
-                S.idv[e] = v;
-            }
         }
         if (lane == 31) S.carry[warp + 1] = rec;
         __syncthreads();
-        if (Policy::AVOID && r0 == 0) {
-            if (tid == 0) resolve_entry0<Policy>(A, S, sb);      // thread 0 settles what happened before the tile
-            __syncthreads();
-        }
         Rec pv = rec_shfl_up(rec);
         int pstart = __shfl_up_sync(0xffffffffu, lstart, 1);
         if (lane == 0) { pv = S.carry[warp]; pstart = -2; }
@@ -941,7 +976,15 @@ __device__ void process_range(const typename Policy::Args &PA, const ScanArgs &A
             bool skipped = false;
             if (Policy::AVOID) {
                 // the line this one is paired with is the last non-skipped line (make_links.py:72-74)
-                if (idv_inv(S.idv[e - 1])) {
+                if (av_fixed) {
+                    skipped = !idv_kept(S.idv[e]);
+                    if (!skipped && !idv_kept(S.idv[e - 1])) {
+                        int j = e - 1;
+                        while (j > 0 && !idv_kept(S.idv[j])) j--;
+                        if (j == 0 && !idv_kept(S.idv[0])) pv = *S.ext;
+                        else pv = parse_any<Policy>(A, S, S.lines[j], sent, trunc, true);
+                    }
+                } else if (idv_inv(S.idv[e - 1])) {
                     int j = e - 1;
                     while (j > 0 && idv_inv(S.idv[j])) j--;
                     int prev = j, pid = idv_id(S.idv[j]);
