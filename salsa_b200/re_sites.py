@@ -63,7 +63,13 @@ def count_sites(eng, fasta, enzyme, timers=None, device_copy=None):
         raise FastaError('sequence line before the first header (the reference raises KeyError, RE_sites.py:22)')
     patterns = None if enzyme == 'DNASE' else expand_enzymes(enzyme)          # validate before any GPU work
     if d is None:
-        d = torch.from_numpy(np.array(fasta, copy=True) if not fasta.flags.writeable else np.ascontiguousarray(fasta)).to(dev)
+        if n > (64 << 20):
+            # a large host array (np.memmap of the assembly, or a rank's byte range of it): through pinned buffers, four
+            # copying threads side by side, instead of a private copy followed by a pageable transfer
+            from .reproject import _stream_in
+            d = _stream_in(None, n, dev, src=np.ascontiguousarray(fasta) if not fasta.flags.c_contiguous else fasta)
+        else:
+            d = torch.from_numpy(np.array(fasta, copy=True) if not fasta.flags.writeable else np.ascontiguousarray(fasta)).to(dev)
 
     def tick(name):
         if timers is not None:

@@ -55,8 +55,8 @@ def _pinned(nbytes, slot):
     return b
 
 
-def _stream_in(rp, size, device):
-    """File -> device.  One reader's copy out of the page cache runs at ~7 GB/s, a tenth of what the host link takes, so
+def _stream_in(rp, size, device, src=None):
+    """File (or, with src, a host uint8 numpy array such as a read-only np.memmap) -> device.  One reader's copy out of the page cache runs at ~7 GB/s, a tenth of what the host link takes, so
     files beyond a few chunks are read by READERS threads side by side (chunks dealt round robin; pread and the copies
     release the GIL), each through its own two pinned 32 MiB buffers and its own stream: the read of a thread's next
     chunk overlaps the copy of its last one."""
@@ -77,7 +77,7 @@ def _stream_in(rp, size, device):
             stream.wait_event(start)
             pin = [_pinned(chunk, 2 * w), _pinned(chunk, 2 * w + 1)]
             ev = [torch.cuda.Event(), torch.cuda.Event()]
-            fd = os.open(rp, os.O_RDONLY)
+            fd = os.open(rp, os.O_RDONLY) if src is None else -1
             try:
                 with torch.cuda.stream(stream):
                     for i, c in enumerate(range(w, nchunk, nthr)):
@@ -87,6 +87,9 @@ def _stream_in(rp, size, device):
                             ev[i & 1].synchronize()           # the copy that last used this buffer is done
                         view = memoryview(pin[i & 1].numpy())[:n]
                         got = 0
+                        if src is not None:
+                            np.copyto(pin[i & 1].numpy()[:n], src[pos:pos + n])      # (releases the GIL)
+                            got = n
                         while got < n:
                             r = os.preadv(fd, [view[got:]], pos + got)
                             if not r:
@@ -96,7 +99,8 @@ def _stream_in(rp, size, device):
                         ev[i & 1].record(stream)
                 stream.synchronize()
             finally:
-                os.close(fd)
+                if fd >= 0:
+                    os.close(fd)
         except Exception as e:                                # raised in the caller's thread below
             errors.append(e)
 
