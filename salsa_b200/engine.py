@@ -191,7 +191,7 @@ class Engine:
         check(self.L.salsa_bed_ingest_dense_host(self.ctx, ptr, n, stage.data_ptr(), chunk_bytes, self.table.data_ptr(),
                                                  self.stats.data_ptr(), torch.cuda.current_stream().cuda_stream))
 
-    def ingest_file(self, path, chunk_bytes=256 << 20):
+    def ingest_file(self, path, chunk_bytes=256 << 20, whole=None):
         """Ingest a BED file from disk (what make_links.py does with -b).  The file
         is memory-mapped and streamed in line-aligned chunks that overlap by one
         line (see salsa_bed_ingest_dense in include/salsa_b200.h)."""
@@ -199,17 +199,20 @@ class Engine:
         size = os.path.getsize(path)
         if size == 0:
             return
-        if self.navoid:
-            # With an avoid list a chunk may only start on a line that can never be skipped (make_links.py:72-74); a BED
-            # whose every scaffold is in some avoid pair has no such line.  A BED that fits the GPU therefore goes there in
-            # one piece (the kernel resolves chains of any length), and only a larger one is cut.
-            free, _ = torch.cuda.mem_get_info(self.device)
-            if size + (256 << 20) < free:
-                from .reproject import _stream_in
-                dev = _stream_in(os.path.realpath(path), size, self.device)
-                self.ingest_device(dev)
-                torch.cuda.current_stream().synchronize()
-                return
+        # A BED that fits the GPU goes there in one piece, through four readers and pinned buffers (a pageable copy out of
+        # the mapping runs at a fraction of the host link); only a larger one is cut into chunks.  With an avoid list this
+        # is also what makes every file ingestible: a chunk may only start on a line that can never be skipped
+        # (make_links.py:72-74), and a BED whose every scaffold is in some avoid pair has no such line, while the kernel
+        # itself resolves chains of any length.
+        free, _ = torch.cuda.mem_get_info(self.device)
+        if whole is None:
+            whole = size + (256 << 20) < free             # (whole=False: the tests' way to the chunked path)
+        if whole:
+            from .reproject import _stream_in
+            dev = _stream_in(os.path.realpath(path), size, self.device)
+            self.ingest_device(dev)
+            torch.cuda.current_stream().synchronize()
+            return
         mm = np.memmap(path, dtype=np.uint8, mode='r')
         if self.mode == 'dense':
             self.ingest_host(mm, chunk_bytes=min(chunk_bytes, 64 << 20))

@@ -197,6 +197,26 @@ def test_100k_contigs_sparse_against_the_oracle(eng, oracle_lib):
     assert got == exp
 
 
+@pytest.mark.parametrize('mode', ['dense', 'sparse'])
+def test_file_ingest_whole_and_chunked(eng, oracle_lib, tmp_path, mode):
+    """Engine.ingest_file: one piece through the pinned readers (the default for a BED that fits the GPU) and the
+    line-aligned chunks a larger file is cut into give the oracle's links."""
+    from salsa_b200 import synth
+    asm, rec, bed = synth.small_case(ncontig=40, genome=800_000, npairs=30000, seed=12, triple=0.05, noise=0.4)
+    want, _ = oracle_dict(oracle_lib, bed, asm.names, asm.lengths)
+    p = str(tmp_path / 'reads.bed')
+    open(p, 'wb').write(bed)
+    n = asm.ncontig
+    for whole in (None, False):
+        eng.set_contigs(asm.names, np.asarray(asm.lengths, np.int64), np.ones(n, np.int64), np.ones(n, np.int64))
+        eng.begin_links(mode, sparse_capacity=1 << 16)
+        eng.ingest_file(p, chunk_bytes=1 << 18, whole=whole)
+        st = eng.stats_read()
+        f, s2, e, c = eng.links()
+        got = {(eng.names[a], eng.names[b], int(x)): int(y) for a, b, x, y in zip(f, s2, e, c)}
+        assert got == want and sum(got.values()) == st.pairs, whole
+
+
 def test_timers_through_the_abi(eng):
     from salsa_b200 import synth
     asm, rec, bed = synth.small_case(ncontig=30, genome=600_000, npairs=20000, seed=5)
