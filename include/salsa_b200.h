@@ -89,7 +89,10 @@ int salsa_timers(salsa_ctx *ctx, double *h_out_ms, uint64_t *h_out_launches, int
  *       is exactly  B <=> start+end <= floor(len)  (DESIGN.md).
  *   h_flags[i]     : SALSA_CTG_* bits.
  * Names that appear only in links_avoid_iteration_N are listed too, without
- * SALSA_CTG_HAS_LEN.  Synchronises.
+ * SALSA_CTG_HAS_LEN.  Synchronises.  Device memory held by the context: the
+ * open-addressing name table (32 bytes per slot; 64 slots per name up to 2^20
+ * slots, at least 2 per name beyond that -- sparse on purpose, a second probe
+ * costs the scanner a whole L2 round trip), 16 bytes per contig and the names.
  */
 #define SALSA_CTG_HAS_LEN 1u
 #define SALSA_CTG_HAS_RE 2u
