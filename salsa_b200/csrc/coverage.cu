@@ -280,7 +280,7 @@ __device__ __forceinline__ Summ summ_shfl_down(const Summ &s, int d)
 constexpr int KT = 64;            // threads per chunk in this kernel
 constexpr int KPER = CH / KT;     // 64
 
-__global__ void __launch_bounds__(KT) kadane_chunk_kernel(const int *cov, const Seg *segs, const uint64_t *seg_chunk_off, int nseg,
+__global__ void __launch_bounds__(KT, 10) kadane_chunk_kernel(const int *cov, const Seg *segs, const uint64_t *seg_chunk_off, int nseg,
                                                           const unsigned long long *seg_sum, Summ *summ)
 {
     __shared__ Summ wres[KT / 32];
