@@ -235,6 +235,25 @@ __device__ __forceinline__ uint32_t cheap16_of(const uint4 &v)
     return pack16(le_bytes_0x2f(v.x), le_bytes_0x2f(v.y), le_bytes_0x2f(v.z), le_bytes_0x2f(v.w));
 }
 
+// special flags (0x80 per special byte) of one word -> newline flags: a special byte has bit 7 clear, so it is '\n' iff the low
+// seven bits of (byte ^ 0x0A) are zero; (y | 0x80) - 1 clears bit 7 exactly then, and no byte borrows from its neighbour.
+// Three instructions per word where the stand-alone equality test takes four.
+__device__ __forceinline__ uint32_t nl_of_special(uint32_t w, uint32_t spf)
+{
+    const uint32_t u = ((w ^ 0x0A0A0A0Au) | 0x80808080u) - 0x01010101u;
+    return ~u & spf;
+}
+template <bool CHEAP>
+__device__ __forceinline__ void masks16(const uint4 &v, uint32_t &sp, uint32_t &nl)
+{
+    const uint32_t f0 = CHEAP ? le_bytes_0x2f(v.x) : (le_bytes_0x20(v.x) | eq_bytes(v.x, 0x2F2F2F2Fu));
+    const uint32_t f1 = CHEAP ? le_bytes_0x2f(v.y) : (le_bytes_0x20(v.y) | eq_bytes(v.y, 0x2F2F2F2Fu));
+    const uint32_t f2 = CHEAP ? le_bytes_0x2f(v.z) : (le_bytes_0x20(v.z) | eq_bytes(v.z, 0x2F2F2F2Fu));
+    const uint32_t f3 = CHEAP ? le_bytes_0x2f(v.w) : (le_bytes_0x20(v.w) | eq_bytes(v.w, 0x2F2F2F2Fu));
+    sp = pack16(f0, f1, f2, f3);
+    nl = pack16(nl_of_special(v.x, f0), nl_of_special(v.y, f1), nl_of_special(v.z, f2), nl_of_special(v.w, f3));
+}
+
 struct CheapTest { static constexpr bool value = true; };
 struct ExactTest { static constexpr bool value = false; };
 
@@ -646,9 +665,10 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
         const uint32_t ro = c & (RING - 1);
         const uint4 *src = reinterpret_cast<const uint4 *>(s + ro);
         const uint4 v0 = src[0], v1 = src[1], v2 = src[2], v3 = src[3];
-        uint32_t mlo = nl16_of(v0) | (nl16_of(v1) << 16), mhi = nl16_of(v2) | (nl16_of(v3) << 16);
-        const uint2 sp = CHEAP ? make_uint2(cheap16_of(v0) | (cheap16_of(v1) << 16), cheap16_of(v2) | (cheap16_of(v3) << 16))
-                               : make_uint2(sp16_of(v0) | (sp16_of(v1) << 16), sp16_of(v2) | (sp16_of(v3) << 16));
+        uint32_t s0, s1, s2, s3, n0, n1, n2, n3;
+        masks16<CHEAP>(v0, s0, n0); masks16<CHEAP>(v1, s1, n1); masks16<CHEAP>(v2, s2, n2); masks16<CHEAP>(v3, s3, n3);
+        uint32_t mlo = n0 | (n1 << 16), mhi = n2 | (n3 << 16);
+        const uint2 sp = make_uint2(s0 | (s1 << 16), s2 | (s3 << 16));
         if (cpos >= nl_lo_r && cpos + (uint32_t)GRP <= nl_hi_r) {  // everywhere but in the chunk's first and last iterations
             *reinterpret_cast<uint2 *>(spw + (ro >> 5)) = sp;
             if (ro < (uint32_t)MIRROR) *reinterpret_cast<uint2 *>(spw + ((RING + ro) >> 5)) = sp;
