@@ -346,7 +346,7 @@ __device__ __forceinline__ int lookup_global(const DevTable &t, const uint8_t *g
 }
 
 template <class Emit>
-__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t chunk_bytes, uint32_t nchunks, const int *d_mode)
+__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t chunk_bytes, uint32_t nchunks, int *d_mode)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -376,9 +376,15 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     const unsigned ltmask = (1u << lane) - 1u;
     const bool cheap = *d_mode != 0;             // which special-byte test (same for the whole launch)
     const unsigned long long dend = A.dend, dend16 = (dend + 15ull) & ~15ull;
-    // Chunks are dealt round robin: at any time the warps of the whole GPU work side by side in one window of the text
-    // (a few hundred MB), which keeps the TLB and the DRAM pages they touch few.
-    for (uint32_t ck = blockIdx.x * WARPS + warp; ck < nchunks; ck += gridDim.x * WARPS) {
+    // Chunks are handed out in file order through one counter (d_mode[1], zeroed before the launch): at any time the warps of
+    // the whole GPU work side by side in one window of the text (a few hundred MB), which keeps the TLB and the DRAM pages they
+    // touch few, and a warp that drew chunks with many candidate pairs simply takes fewer of them (dealing them round robin
+    // left the last of 61 rounds 40 % empty).
+    for (;;) {
+    uint32_t ck = 0;
+    if (lane == 0) ck = (uint32_t)atomicAdd(d_mode + 1, 1);
+    ck = __shfl_sync(0xffffffffu, ck, 0);
+    if (ck >= nchunks) break;
     // ---- the chunk, in abase coordinates ----
     const unsigned long long S0 = (unsigned long long)ck * chunk_bytes;
     unsigned long long S1 = S0 + chunk_bytes;
@@ -814,6 +820,7 @@ int launch_stream(const typename Emit::Args &EA, const DevTable &t, const void *
     // scan_mode: 0 = the sample kernel decides, 1 = exact special-byte test, 2 = cheap one
     if (scan_mode == 0) bed_sample_kernel<<<1, 256, 0, st>>>(A, names_punct, d_mode);
     else CUDA_TRY(cudaMemsetAsync(d_mode, scan_mode == 2 ? 1 : 0, 1, st));
+    CUDA_TRY(cudaMemsetAsync(d_mode + 1, 0, sizeof(int), st));          // the chunk counter
     bed_stream_kernel<Emit><<<(unsigned)ctas, WARPS * 32, CTA_SMEM, st>>>(EA, A, (uint32_t)cb, (uint32_t)nchunks, d_mode);
     CUDA_TRY(cudaGetLastError());
     return SALSA_OK;
