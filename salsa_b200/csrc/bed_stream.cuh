@@ -1,26 +1,30 @@
 // bed_stream.cuh -- the streaming BED scanner of the link histogram (make_links.py:60-146).
 //
 // Where bed_scan.cuh cuts the text into tiles that CTAs pick up one by one, this kernel is
-// PERSISTENT and WARP-AUTONOMOUS: the buffer is cut into as many contiguous byte streams as there
-// are resident warps, and every warp walks its stream from start to end through a private ring in
-// shared memory that it fills itself with 1-D TMA bulk copies (cp.async.bulk + mbarrier, a few
-// stages ahead).  There is no block-wide barrier, no halo that is classified twice, no per-tile
-// prologue, and the "previous line" simply travels along the stream.
+// PERSISTENT and WARP-AUTONOMOUS: the buffer is cut into 256 KiB chunks that the resident warps
+// draw, in file order, from one atomic counter, and every warp walks its chunk from start to end
+// through a private 8 KiB ring in shared memory that it fills itself with cp.async (LDGSTS.128,
+// 16 bytes per lane, L1 bypassed; 2 KiB groups, up to three in flight).  There is no block-wide
+// barrier, no halo that is classified twice, no per-tile prologue, and the "previous line" simply
+// travels along the chunk.  (A first version staged the ring with one 1-D TMA bulk copy + mbarrier
+// per warp and stage: the elected-lane issue sequence cost more instructions than 32 lanes x 16 B.)
 //
 // Per warp, three interleaved activities:
-//   CLASSIFY  1 KiB per iteration (32 B per lane): exact SWAR byte tests + dp4a bit packing give
-//             the "special" bitmap (<= 0x20 or '/', one bit per ring byte) and the newline mask;
-//             line starts are ranked by ballot and appended to a small ring of line starts.
+//   CLASSIFY  2 KiB per iteration (64 B per lane): SWAR byte tests + dp4a bit packing give the
+//             "special" bitmap (one bit per ring byte: <= 0x20 or '/', or the cheaper superset
+//             <= 0x2F when a sample of the text allows it) and, from the same flags, the newline
+//             mask; line starts are ranked by ballot and appended to a small ring of line starts.
 //   PHASE 1   32 lines per step, one lane per line: the four field boundaries from the special
 //             bitmap, separator bytes checked, the contig name as a masked 16-byte window, the
 //             last four bytes of read.split('/')[0].  A pair of plain lines whose names are equal
 //             or whose read names provably differ is dropped here (exactly the pairs the
-//             reference neither counts nor dies on); everything else is queued.
-//   PHASE 2   16 queued pairs at a time, two lanes per pair (one line each): name -> id through
-//             the device hash table, start/end by dp4a digit conversion, full read-name compare,
-//             then the reference's checks in the reference's order and one RED into the table.
-//             A line that is not of the plain form is parsed by the byte-loop parser straight
-//             from global memory (str.split() in full): identical results, only slower.
+//             reference neither counts nor dies on); everything else is queued (16 bytes).
+//   PHASE 2   16 queued pairs at a time, two lanes per pair (one line each), the lines re-read
+//             from global memory (L2): name -> id through the device hash table, start/end by
+//             dp4a digit conversion, full read-name compare, then the reference's checks in the
+//             reference's order and one RED into the table.  A line that is not of the plain form
+//             is parsed by the byte-loop parser straight from global memory (str.split() in
+//             full): identical results, only slower.
 #pragma once
 #include "bed_scan.cuh"
 
