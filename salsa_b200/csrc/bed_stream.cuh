@@ -350,7 +350,7 @@ __device__ __forceinline__ int lookup_global(const DevTable &t, const uint8_t *g
 }
 
 template <class Emit>
-__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t chunk_bytes, uint32_t nchunks, int *d_mode)
+__global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::Args EA, ScanArgs A, uint32_t unit_bytes, uint32_t nunits, uint32_t take_big, uint32_t tail_units, int *d_mode)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -385,14 +385,21 @@ __global__ void __launch_bounds__(WARPS * 32) bed_stream_kernel(typename Emit::A
     // touch few, and a warp that drew chunks with many candidate pairs simply takes fewer of them (dealing them round robin
     // left the last of 61 rounds 40 % empty).
     for (;;) {
-    uint32_t ck = 0;
-    if (lane == 0) ck = (uint32_t)atomicAdd(d_mode + 1, 1);
+    // a chunk = take_big units while plenty of text is left, one unit over the last tail_units: the warps then finish
+    // within a quarter of a chunk's time of one another (any cut at unit boundaries is a valid set of chunks)
+    uint32_t ck = 0, take = 1;
+    if (lane == 0) {
+        const uint32_t seen = (uint32_t)*((volatile int *)(d_mode + 1));
+        take = (seen < nunits && nunits - seen > tail_units) ? take_big : 1u;
+        ck = (uint32_t)atomicAdd(d_mode + 1, (int)take);
+    }
     ck = __shfl_sync(0xffffffffu, ck, 0);
-    if (ck >= nchunks) break;
+    take = __shfl_sync(0xffffffffu, take, 0);
+    if (ck >= nunits) break;
     // ---- the chunk, in abase coordinates ----
-    const unsigned long long S0 = (unsigned long long)ck * chunk_bytes;
-    unsigned long long S1 = S0 + chunk_bytes;
-    if (S1 > dend || ck + 1 == nchunks) S1 = dend;
+    const unsigned long long S0 = (unsigned long long)ck * unit_bytes;
+    unsigned long long S1 = S0 + (unsigned long long)take * unit_bytes;
+    if (S1 > dend || ck + take >= nunits) S1 = dend;
     unsigned long long lo = S0 >= (unsigned long long)HALO ? S0 - HALO : 0ull;            // first byte loaded
     asm volatile("" : "+l"(lo));             // (kept in registers: see lane / warp above)
     unsigned long long hi = S1 + HALO;                                                    // one past the last byte classified
@@ -821,11 +828,21 @@ int launch_stream(const typename Emit::Args &EA, const DevTable &t, const void *
     if (nchunks > 0x7fffffffull) SALSA_FAIL(SALSA_ERR_ARG, "BED chunk too large (%zu bytes)", nbytes);
     uint64_t ctas = (nchunks + WARPS - 1) / WARPS;
     if (ctas > (uint64_t)ctas_per_dev[dev]) ctas = (uint64_t)ctas_per_dev[dev];
+    // large inputs: the counter hands out quarter chunks, four at a time until the text is nearly used up, then singly
+    uint64_t unit = cb, take_big = 1, tail_units = 0;
+    if (cb == CHUNK_MAX && nchunks > 8 * nwarps) {
+        unit = cb / 4;
+        take_big = 4;
+        tail_units = 8 * nwarps;                        // the last two chunks' worth per warp
+    }
+    const uint64_t nunits = (A.dend + unit - 1) / unit;
+    if (nunits > 0x3fffffffull) SALSA_FAIL(SALSA_ERR_ARG, "BED chunk too large (%zu bytes)", nbytes);
     // scan_mode: 0 = the sample kernel decides, 1 = exact special-byte test, 2 = cheap one
     if (scan_mode == 0) bed_sample_kernel<<<1, 256, 0, st>>>(A, names_punct, d_mode);
     else CUDA_TRY(cudaMemsetAsync(d_mode, scan_mode == 2 ? 1 : 0, 1, st));
     CUDA_TRY(cudaMemsetAsync(d_mode + 1, 0, sizeof(int), st));          // the chunk counter
-    bed_stream_kernel<Emit><<<(unsigned)ctas, WARPS * 32, CTA_SMEM, st>>>(EA, A, (uint32_t)cb, (uint32_t)nchunks, d_mode);
+    bed_stream_kernel<Emit><<<(unsigned)ctas, WARPS * 32, CTA_SMEM, st>>>(EA, A, (uint32_t)unit, (uint32_t)nunits, (uint32_t)take_big, (uint32_t)tail_units,
+                                                                         d_mode);
     CUDA_TRY(cudaGetLastError());
     return SALSA_OK;
 }
