@@ -40,8 +40,8 @@ def emit(line):
 
 def ncu_traffic_ratio():
     """dram bytes (read + write) / algorithmic bytes of the ingest kernel, from the committed
-    `ncu --set full` capture (profiles/r02_v6_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
-    p = os.path.join(ROOT, 'profiles', 'r02_v6_ingest_metrics.txt')
+    `ncu --set full` capture (profiles/r02_v8_ingest_metrics.txt, 50 M-pair launch = 4,703,357,292 B)."""
+    p = os.path.join(ROOT, 'profiles', 'r02_v8_ingest_metrics.txt')
     try:
         rd = wr = None
         for ln in open(p):
@@ -451,7 +451,7 @@ def run_ours(args):
                    'parity_full_size': 'table == generator expected table: %s; counted pairs %d' % (parity, stt.pairs)},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'traffic': (ncu_traffic_ratio() * bed_bytes) if ncu_traffic_ratio() else None,
-                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r02_v6_ingest_metrics.txt), '
+                     'traffic_source': 'ncu --set full dram read+write of a 4.70 GB launch (profiles/r02_v8_ingest_metrics.txt), '
                                        'scaled to this launch by algorithmic bytes',
                      'peak_source': which + ' (MEASURED_PEAKS.json hbm_gbs, burst copy)',
                      'kernel': 'bedstream::bed_stream_kernel<LinkEmit<dense>>', 'algorithmic_bytes_per_launch': bed_bytes,
